@@ -1,0 +1,151 @@
+"""CPU oracle for Rosella's hot path — TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this package.  ``rosella_b200`` never does.
+See ``oracle/oracle.h`` for the parity status of each function.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+NBINS = 136
+RUST, FLIGHT = 0, 1
+TNF, DEPTH = 0, 1
+
+
+def build(force: bool = False) -> str:
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_tnf.c", "oracle_metrics.c", "oracle_knn.c", "oracle.h")]
+    if force or not os.path.exists(_LIB_PATH) or any(
+        os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs
+    ):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "liboracle.so"])
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            build()
+        _lib = C.CDLL(_LIB_PATH)
+        _lib.orc_normalize.restype = C.c_size_t
+        for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat"):
+            getattr(_lib, f).restype = C.c_double
+        for f in ("orc_tnf_distance_f32", "orc_depth_distance_f32"):
+            getattr(_lib, f).restype = C.c_float
+    return _lib
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def canonical_kmers() -> list[str]:
+    buf = np.zeros(NBINS * 4, np.uint8)
+    lib().orc_canonical_kmers(_p(buf, C.c_uint8))
+    return [bytes(buf[4 * i:4 * i + 4]).decode() for i in range(NBINS)]
+
+
+def code_to_bin() -> np.ndarray:
+    lut = np.zeros(256, np.uint8)
+    lib().orc_code_to_bin(_p(lut, C.c_uint8))
+    return lut
+
+
+def normalize(seq: bytes) -> bytes:
+    a = np.frombuffer(seq, np.uint8)
+    out = np.zeros(max(len(a), 1), np.uint8)
+    n = lib().orc_normalize(_p(a, C.c_uint8), C.c_size_t(len(a)), _p(out, C.c_uint8))
+    return bytes(out[:n])
+
+
+def tnf_count(seq: np.ndarray, offsets: np.ndarray, fast: bool = False, threads: int = 0):
+    """-> (counts u32[n,136], n_kmers u64[n], freqs f64[n,136])"""
+    seq = np.ascontiguousarray(seq, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    n = len(offsets) - 1
+    counts = np.zeros((n, NBINS), np.uint32)
+    nk = np.zeros(n, np.uint64)
+    freqs = np.zeros((n, NBINS), np.float64)
+    args = [_p(seq, C.c_uint8), _p(offsets, C.c_uint64), C.c_uint64(n),
+            _p(counts, C.c_uint32), _p(nk, C.c_uint64), _p(freqs, C.c_double)]
+    if fast:
+        lib().orc_tnf_count_fast(*args, C.c_int(threads))
+    else:
+        lib().orc_tnf_count(*args)
+    return counts, nk, freqs
+
+
+def clr(x: np.ndarray, variant: int = RUST) -> np.ndarray:
+    x = np.ascontiguousarray(x, np.float64)
+    out = np.empty_like(x)
+    f = lib().orc_clr_flight if variant == FLIGHT else lib().orc_clr
+    f(_p(x, C.c_double), _p(out, C.c_double), C.c_uint64(x.shape[0]), C.c_uint32(x.shape[1]))
+    return out
+
+
+def kmer_correlation(x, y) -> float:
+    x = np.ascontiguousarray(x, np.float64); y = np.ascontiguousarray(y, np.float64)
+    return lib().orc_kmer_correlation(_p(x, C.c_double), _p(y, C.c_double), C.c_uint32(len(x)))
+
+
+def rho_flight(x, y) -> float:
+    x = np.ascontiguousarray(x, np.float64); y = np.ascontiguousarray(y, np.float64)
+    return lib().orc_rho_flight(_p(x, C.c_double), _p(y, C.c_double), C.c_uint32(len(x)))
+
+
+def tnf_euclidean(x, y) -> float:
+    x = np.ascontiguousarray(x, np.float64); y = np.ascontiguousarray(y, np.float64)
+    return lib().orc_tnf_euclidean(_p(x, C.c_double), _p(y, C.c_double), C.c_uint32(len(x)))
+
+
+def metabat(a, b, variant: int = RUST) -> float:
+    a = np.ascontiguousarray(a, np.float64); b = np.ascontiguousarray(b, np.float64)
+    return lib().orc_metabat(_p(a, C.c_double), _p(b, C.c_double), C.c_uint32(len(a) // 2), C.c_int(variant))
+
+
+def knn(data: np.ndarray, which: int, k: int, variant: int = RUST, qrows=None, threads: int = 0):
+    """Exhaustive exact top-k.  -> (idx u32[nq,k], dist f32[nq,k], dist64 f64[nq,k])"""
+    data = np.ascontiguousarray(data, np.float64)
+    n, w = data.shape
+    if qrows is None:
+        nq, qp = n, None
+    else:
+        qrows = np.ascontiguousarray(qrows, np.uint64)
+        nq, qp = len(qrows), _p(qrows, C.c_uint64)
+    idx = np.zeros((nq, k), np.uint32)
+    dist = np.zeros((nq, k), np.float32)
+    d64 = np.zeros((nq, k), np.float64)
+    lib().orc_knn(_p(data, C.c_double), C.c_uint64(n), C.c_uint32(w), C.c_int(which), C.c_int(variant),
+                  qp, C.c_uint64(nq), C.c_uint32(k), _p(idx, C.c_uint32), _p(dist, C.c_float),
+                  _p(d64, C.c_double), C.c_int(threads))
+    return idx, dist, d64
+
+
+def mutual_knn(idx: np.ndarray, keep_n_edges: int) -> np.ndarray:
+    idx = np.ascontiguousarray(idx, np.uint32)
+    keep = np.zeros(idx.shape, np.uint8)
+    lib().orc_mutual_knn(_p(idx, C.c_uint32), C.c_uint64(idx.shape[0]), C.c_uint32(idx.shape[1]),
+                         C.c_uint32(keep_n_edges), _p(keep, C.c_uint8))
+    return keep
+
+
+def intersect(base: np.ndarray, other: np.ndarray, keep_n_edges: int) -> np.ndarray:
+    base = np.ascontiguousarray(base, np.uint32); other = np.ascontiguousarray(other, np.uint32)
+    keep = np.zeros(base.shape, np.uint8)
+    lib().orc_intersect(_p(base, C.c_uint32), _p(other, C.c_uint32), C.c_uint64(base.shape[0]),
+                        C.c_uint32(base.shape[1]), C.c_uint32(keep_n_edges), _p(keep, C.c_uint8))
+    return keep
+
+
+def max_threads() -> int:
+    return lib().orc_max_threads()
