@@ -1,0 +1,216 @@
+#!/usr/bin/env python
+"""bench.py — the driver's benchmark contract for the kNN-graph hot path (+ TNF counting as extra keys).
+
+Workload (BASELINE.json configs[2]): synthetic 1M contigs x (136 TNF + 50 coverage samples), k=30.
+A "step" = one pass of the hot path over one batch of `--query-rows` query contigs per GPU against ALL
+n reference contigs: both kNN graphs (depth + TNF), i.e. FP32 select kernels + f64 re-evaluation, and
+for N>1 the NCCL all-gather of the per-rank slabs.  Cost is linear in query rows, so
+contigs/s = rows per step / step time is the throughput of the full 1M-row build.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=1_000_000, help="contigs (reference rows)")
+    ap.add_argument("--samples", type=int, default=50)
+    ap.add_argument("--k", type=int, default=30)
+    ap.add_argument("--query-rows", type=int, default=0, help="query rows per GPU per step (0 = 2 waves of CTAs)")
+    ap.add_argument("--tnf-gbp", type=float, default=-1.0, help="TNF counting set in Gbp (-1 = auto, 0 = skip)")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nme, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------- workload
+def algorithmic_flops(cov_q: np.ndarray, cov_all_absent: np.ndarray, n: int, graphs_tnf: int = 1) -> float:
+    """SURVEY §8d convention: F = pairs * 2*136 * n_tnf_metrics + A * 140, A = contributing
+    (ordered pair, sample) triples = sum_s (Q*n - zq_s * z_s), z = rows absent in sample s."""
+    q = cov_q.shape[0]
+    zq = (cov_q[:, 0::2] <= 0).sum(axis=0).astype(np.float64)
+    a = float((q * float(n) - zq * cov_all_absent).sum())
+    return float(q) * n * 272.0 * graphs_tnf + a * 140.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d.get("hbm_gbs", 6650.0), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def fp32_peak_tflops():
+    """Live FFMA micro-benchmark (rosella_b200/build/microbench); MEASURED_PEAKS.json has no FP32 entry."""
+    exe = os.path.join(ROOT, "rosella_b200", "build", "microbench")
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout
+        d = json.loads(out)
+        return d["ffma_tflops"], d
+    except Exception as e:  # noqa: BLE001
+        return None, {"error": str(e)}
+
+
+def workload_config(args, q_rows, world):
+    return {"workload": f"synthetic {args.n} contigs x (136 TNF + {args.samples} coverage samples), k={args.k}: "
+                        "exact depth + TNF kNN graphs (BASELINE.json configs[2])",
+            "n_contigs": args.n, "tnf_bins": 136, "coverage_samples": args.samples, "k": args.k,
+            "query_rows_per_gpu_per_step": q_rows, "sharding": f"query rows over {world} rank(s), references replicated",
+            "variant": "rust (coverage_calculator.rs:582-666, kmer_counting.rs:366-414)",
+            "l2": "256 MB buffer zeroed between timed iterations; reference set (1.3 GB FP32) exceeds L2"}
+
+
+def main_reference(args):
+    """--impl reference: the reference's own CPU path for this workload, timed on the host cores.
+    The reference (Rust) cannot be built here or on the GPU box, so this is the oracle port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from benchmarks import cpu_arm
+    from rosella_b200 import synth
+    tnf, cov, _ = synth.knn_tables(args.n, args.samples)
+    vals, samples = [], []
+    budget = max(2.0, min(args.cpu_seconds, 120.0 / max(args.steps + args.warmup, 1)))
+    for i in range(args.warmup + args.steps):
+        r = cpu_arm.knn_sample(tnf, cov, args.k, budget)
+        if i >= args.warmup:
+            vals.append(r["value"]); samples.append(r)
+    v = float(np.mean(vals))
+    last = samples[-1]
+    line = {"impl": "reference", "metric": "kNN-graph contigs/s", "value": v, "unit": "contigs/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * last["seconds"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, last["rows"], 1),
+            "cpu_baseline": {"value": v, "unit": "contigs/s", "cores": last["cores"], "kind": "port",
+                             "sample": last["sample"]},
+            "e2e": {"value": v, "unit": "contigs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main_ours(args):
+    from benchmarks import cpu_arm, knn_arm, tnf_arm
+    helpers = sys.modules[__name__]
+    r = knn_arm.run(args, helpers)
+    if r["rank"] != 0:
+        return
+    world, q_rows = r["world"], r["q_rows"]
+    step_s = r["total_ms"] / args.steps * 1e-3
+    value = world * q_rows / step_s
+    e2e_value = world * q_rows / (r["e2e_total_ms"] / args.steps * 1e-3)
+    pk = peaks()
+    fp32, micro = fp32_peak_tflops()
+    ach = r["flops_depth"] / (r["depth_sel_ms"] * 1e-3) / 1e12
+    line = {
+        "metric": "kNN-graph contigs/s", "value": value, "unit": "contigs/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 select + f64 re-evaluation", "data": "synthetic",
+        "config": workload_config(args, q_rows, world),
+        "e2e": {"value": e2e_value, "unit": "contigs/s", "h2d_bytes_per_step": r["h2d_per_step"],
+                "d2h_bytes_per_step": r["d2h_per_step"],
+                "note": "every step re-loads both f64 tables from pinned host memory (rg_knn_load) and returns host lists"},
+        "gpu_launches": r["launches"], "clocks": r["clocks"],
+        "roofline": {"kernel": "depth_select_kernel", "bound": "fp32", "achieved": ach, "peak": fp32,
+                     "unit": "TFLOP/s", "frac": (ach / fp32) if fp32 else None, "traffic": None,
+                     "peak_source": "live FFMA micro-benchmark (rosella_b200/csrc/microbench.cu); MEASURED_PEAKS.json has no FP32 CUDA-core entry",
+                     "algorithmic_flops_per_launch": r["flops_depth"], "launch_ms": r["depth_sel_ms"]},
+        "kernels_ms": {"depth_select": r["depth_sel_ms"], "depth_rescore": r["depth_res_ms"],
+                       "tnf_select": r["tnf_sel_ms"], "tnf_rescore": r["tnf_res_ms"],
+                       "tnf_select_tflops": r["flops_tnf"] / (r["tnf_sel_ms"] * 1e-3) / 1e12,
+                       "load_h2d": r["load_h2d_ms"], "load_transform": r["load_transform_ms"]},
+        "full_build_seconds_est": args.n / value,
+        "microbench": micro,
+    }
+    tnf, cov = r["tables"]
+    if world == 1:
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()
+                                    if k in ("value", "unit", "cores", "kind", "sample")}
+        gbp = args.tnf_gbp
+        if gbp < 0:
+            import psutil
+            gbp = 10.0 if psutil.virtual_memory().available > 96e9 else 2.0
+        if gbp > 0:
+            del tnf, cov
+            t = tnf_arm.run(r["ctx"], int(gbp * 1e9), args.steps, args.warmup, pk["hbm_gbs"], min(32, os.cpu_count() or 8))
+            seq, offs = t.pop("sample")
+            t["roofline"]["peak_source"] = pk["source"]
+            if not args.no_cpu_baseline:
+                t["cpu_baseline"] = cpu_arm.tnf_sample(seq, offs, args.cpu_seconds)
+            line["tnf"] = t
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        main_reference(a)
+    else:
+        main_ours(a)

@@ -1,0 +1,149 @@
+/*
+ * rosella_gpu.h — C ABI of librosella_gpu.so: Rosella's data-parallel hot path on one B200.
+ *
+ * Drop-in boundary.  Each entry point names the reference interface it
+ * replaces (paths relative to the rosella repository):
+ *
+ *   rg_tnf_*   replace the body of KmerCounter::run            src/kmers/kmer_counting.rs:41-123
+ *              (per-record loop :64-109; canonical index :132-169)
+ *   rg_knn_*   replace EmbedderEngine::build_mutual_kgraph     src/embedding/embedder.rs:31-86
+ *              with the metrics TNFDistance::eval :108-127  (KmerCorrelation::distance,
+ *              src/kmers/kmer_counting.rs:366-414) and DepthDistance::eval :133-171
+ *              (MetabatDistance::distance, src/coverage/coverage_calculator.rs:588-666)
+ *   rg_graph_* compute what mutual_knn / intersect compute    src/graphs/nearest_neighbour_graph.rs:12-72
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every host buffer; the library never keeps
+ *     a caller pointer after a call returns; device memory belongs to the handle.
+ *   - every function returns 0 on success or a negative rg_status; rg_last_error() has the text.
+ *     No exception, abort() or exit() crosses the boundary.
+ *   - NO CPU FALLBACK: without an sm_100 device rg_create fails with RG_ERR_NO_DEVICE.
+ *   - a handle serves one caller thread at a time (the reference calls both entry points from
+ *     its single pipeline thread, recover_engine.rs:111,:510).
+ *   - one handle = one GPU.  Multi-GPU = one handle (process) per GPU, query rows sharded with
+ *     [q_begin, q_end); the per-rank slabs are concatenated by the caller (NCCL all-gather on the
+ *     *_dev outputs, or host concatenation).
+ */
+#ifndef ROSELLA_GPU_H
+#define ROSELLA_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RG_NBINS 136u          /* canonical 4-mers, kmer_counting.rs:11,:132-169 */
+#define RG_ABI_VERSION 1
+
+typedef struct rg_handle rg_handle;
+
+typedef enum {
+    RG_OK = 0,
+    RG_ERR_NO_DEVICE = -1,     /* no CUDA device, or not compute capability 10.x */
+    RG_ERR_INVALID = -2,       /* bad argument (null pointer, k == 0, shapes, non-finite coverage) */
+    RG_ERR_CUDA = -3,          /* CUDA runtime error; text in rg_last_error */
+    RG_ERR_OOM = -4,           /* device or host allocation failed */
+    RG_ERR_STATE = -5          /* call order (e.g. search before load) */
+} rg_status;
+
+/* metric variant: which reference code the arithmetic follows */
+#define RG_VARIANT_RUST 0u     /* coverage_calculator.rs:582-666 + kmer_counting.rs:366-414 */
+#define RG_VARIANT_FLIGHT 1u   /* flight/flight/metrics.py:445-558 (metabat_distance_nn), :601-645 (rho) */
+
+/* which kNN list */
+#define RG_GRAPH_TNF 0u        /* TNFDistance,   embedder.rs:41-48 (tnf_nn) */
+#define RG_GRAPH_DEPTH 1u      /* DepthDistance, embedder.rs:32-39 (depth_nn); MinHash factor = 1 */
+
+/* ------------------------------------------------------------------ lifecycle */
+int32_t rg_abi_version(void);
+int32_t rg_create(int32_t device_id, rg_handle **out);
+void rg_destroy(rg_handle *h);
+/* message of the last failing call on h (h == NULL: last failing rg_create on this thread) */
+const char *rg_last_error(const rg_handle *h);
+int32_t rg_sync(rg_handle *h);
+/* the CUDA stream (cudaStream_t) all of the handle's work is issued on */
+void *rg_stream(rg_handle *h);
+
+/* ------------------------------------------------------------------ TNF counting */
+/* the 136 canonical 4-mers in bin order, 4 bytes each, no terminator (host only) */
+int32_t rg_tnf_canonical_kmers(uint8_t *names /* 136*4 */);
+
+/* Raw record bytes exactly as needletail yields them (may hold newlines, lower case, U, IUPAC,
+ * gaps); record i = seq[offsets[i] .. offsets[i+1]).  Semantics of kmer_counting.rs:64-109:
+ * counts[i*136+b] = occurrences of canonical 4-mer b, n_kmers[i] = counted windows,
+ * freqs = count / n_kmers as f64 (NaN row when n_kmers == 0).  freqs may be NULL. */
+int32_t rg_tnf_count_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n,
+                           uint32_t *counts, uint64_t *n_kmers, double *freqs);
+
+/* Packed layout streamed by the counting kernel: per record, normalised bases (whitespace
+ * removed) 2 bits each, A=0 C=1 G=2 T=3, base j of a 32-base group in bits [2j, 2j+2) of a
+ * uint64 word; validity 1 bit per base (1 = A/C/G/T) in a uint32 word; every record starts on a
+ * word boundary, padding bases are invalid.  word_offsets has n+1 entries. */
+uint64_t rg_tnf_packed_words(const uint8_t *seq, const uint64_t *offsets, uint64_t n);
+int32_t rg_tnf_pack_host(const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint64_t *codes,
+                         uint32_t *valid, uint64_t *word_offsets, int32_t threads);
+int32_t rg_tnf_count_packed(rg_handle *h, const uint64_t *codes, const uint32_t *valid,
+                            const uint64_t *word_offsets, uint64_t n, uint32_t *counts,
+                            uint64_t *n_kmers, double *freqs);
+
+/* staged form (inputs resident in HBM between calls) */
+int32_t rg_tnf_load_packed(rg_handle *h, const uint64_t *codes, const uint32_t *valid,
+                           const uint64_t *word_offsets, uint64_t n);
+int32_t rg_tnf_load_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n);
+int32_t rg_tnf_count_resident(rg_handle *h);   /* async on rg_stream; result stays on device */
+int32_t rg_tnf_fetch(rg_handle *h, uint32_t *counts, uint64_t *n_kmers, double *freqs);
+
+/* ------------------------------------------------------------------ kNN graph */
+/* Copy the two tables to the device and pre-transform them.
+ *   tnf  n x d f64 row-major, exactly the rows Rust hands to TNFDistance (already CLR'd under
+ *        no_flight, kmer_counting.rs:322-323); d must be 136.
+ *   cov  n x 2s f64 row-major, interleaved mean,var per sample as MetabatDistance reads them
+ *        (coverage_calculator.rs:593-596).
+ * Either may be NULL if that graph is never searched.  Non-finite coverage -> RG_ERR_INVALID
+ * (the reference panics in Normal::new, coverage_calculator.rs:639). */
+int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                    uint32_t s, uint32_t variant);
+
+/* Exact top-k of query rows [q_begin, q_end) against all n loaded rows, self excluded, ascending
+ * by (f32 distance, index).  idx/dist: (q_end-q_begin) x k; rows with fewer than k candidates are
+ * padded with UINT32_MAX / +inf; n_valid (may be NULL) gets the count per row.
+ * Distances are the reference metric evaluated in f64 and truncated to f32 (embedder.rs:125,:170). */
+int32_t rg_knn_search(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_begin, uint64_t q_end,
+                      uint32_t *idx, float *dist, uint32_t *n_valid);
+/* same, outputs are DEVICE pointers; asynchronous on rg_stream(h) */
+int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_begin, uint64_t q_end,
+                          uint32_t *idx_dev, float *dist_dev, uint32_t *n_valid_dev);
+
+/* one call: load + search of all rows for the graphs in which_mask (bit RG_GRAPH_*);
+ * outputs per graph may be NULL when its bit is clear. */
+int32_t rg_knn_build(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                     uint32_t s, uint32_t k, uint32_t variant, uint32_t which_mask,
+                     uint32_t *tnf_idx, float *tnf_dist, uint32_t *depth_idx, float *depth_dist);
+
+/* ------------------------------------------------------------------ graph post-ops */
+/* keep[i*k+j] = 1 when edge j of node i survives mutual_knn / intersect
+ * (nearest_neighbour_graph.rs:12-35 / :38-72; the reference computes these lists and then drops
+ * them, SURVEY F5 — callers choose whether to apply them).  Host buffers. */
+int32_t rg_graph_mutual(rg_handle *h, const uint32_t *idx, uint64_t n, uint32_t k,
+                        uint32_t keep_n_edges, uint8_t *keep);
+int32_t rg_graph_intersect(rg_handle *h, const uint32_t *base_idx, const uint32_t *other_idx,
+                           uint64_t n, uint32_t k, uint32_t keep_n_edges, uint8_t *keep);
+
+/* ------------------------------------------------------------------ instrumentation */
+typedef struct {
+    double h2d_ms;           /* last load: host->device copies */
+    double transform_ms;     /* last load: pre-transform kernels */
+    double select_ms;        /* last search: fused distance + top-k' kernel (device time) */
+    double rescore_ms;       /* last search: f64 re-evaluation + final sort kernel */
+    double d2h_ms;           /* last search / fetch: device->host copies */
+    double tnf_count_ms;     /* last TNF counting kernel (device time) */
+    uint64_t kernel_launches; /* kernels launched by this handle since creation */
+    uint64_t h2d_bytes, d2h_bytes; /* since creation */
+} rg_timings;
+int32_t rg_get_timings(rg_handle *h, rg_timings *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROSELLA_GPU_H */

@@ -30,7 +30,7 @@ void orc_knn(const double *data, uint64_t n, uint32_t width, int which, int vari
     {
         cand_t *best = (cand_t *)malloc(sizeof(cand_t) * (k + 1));
 #ifdef _OPENMP
-#pragma omp for schedule(dynamic, 4)
+#pragma omp for schedule(dynamic, 1)
 #endif
         for (int64_t qi = 0; qi < (int64_t)nq; ++qi) {
             uint64_t q = qrows ? qrows[qi] : (uint64_t)qi;

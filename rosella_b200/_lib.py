@@ -1,0 +1,97 @@
+"""ctypes binding of librosella_gpu.so (include/rosella_gpu.h).  No CPU fallback: a missing library
+or a missing sm_100 device raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librosella_gpu.so")
+NBINS = 136
+VARIANT_RUST, VARIANT_FLIGHT = 0, 1
+GRAPH_TNF, GRAPH_DEPTH = 0, 1
+
+# every symbol include/rosella_gpu.h declares (tests check the .so exports exactly these)
+SYMBOLS = [
+    "rg_abi_version", "rg_create", "rg_destroy", "rg_last_error", "rg_sync", "rg_stream",
+    "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
+    "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
+    "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
+    "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings",
+]
+
+
+class Timings(C.Structure):
+    _fields_ = [("h2d_ms", C.c_double), ("transform_ms", C.c_double), ("select_ms", C.c_double),
+                ("rescore_ms", C.c_double), ("d2h_ms", C.c_double), ("tnf_count_ms", C.c_double),
+                ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RosellaGpuError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"librosella_gpu error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m rosella_b200.build` "
+            "(there is no CPU fallback for the GPU path)")
+    lib = C.CDLL(LIB_PATH)
+    vp, u8p, u32p, u64p, f32p, f64p = (C.c_void_p, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32),
+                                       C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_double))
+    sig = {
+        "rg_abi_version": (C.c_int32, []),
+        "rg_create": (C.c_int32, [C.c_int32, C.POINTER(vp)]),
+        "rg_destroy": (None, [vp]),
+        "rg_last_error": (C.c_char_p, [vp]),
+        "rg_sync": (C.c_int32, [vp]),
+        "rg_stream": (vp, [vp]),
+        "rg_tnf_canonical_kmers": (C.c_int32, [u8p]),
+        "rg_tnf_count_ascii": (C.c_int32, [vp, u8p, u64p, C.c_uint64, u32p, u64p, f64p]),
+        "rg_tnf_packed_words": (C.c_uint64, [u8p, u64p, C.c_uint64]),
+        "rg_tnf_pack_host": (C.c_int32, [u8p, u64p, C.c_uint64, u64p, u32p, u64p, C.c_int32]),
+        "rg_tnf_count_packed": (C.c_int32, [vp, u64p, u32p, u64p, C.c_uint64, u32p, u64p, f64p]),
+        "rg_tnf_load_packed": (C.c_int32, [vp, u64p, u32p, u64p, C.c_uint64]),
+        "rg_tnf_load_ascii": (C.c_int32, [vp, u8p, u64p, C.c_uint64]),
+        "rg_tnf_count_resident": (C.c_int32, [vp]),
+        "rg_tnf_fetch": (C.c_int32, [vp, u32p, u64p, f64p]),
+        "rg_knn_load": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
+        "rg_knn_search": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, u32p, f32p, u32p]),
+        "rg_knn_search_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, vp, vp, vp]),
+        "rg_knn_build": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                     C.c_uint32, u32p, f32p, u32p, f32p]),
+        "rg_graph_mutual": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
+        "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
+        "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def ptr(a, ctype):
+    """ctypes pointer to a C-contiguous numpy array (None -> NULL)."""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+def as_f64(a):
+    return None if a is None else np.ascontiguousarray(a, np.float64)

@@ -1,0 +1,143 @@
+// knn_transform.cu — rg_knn_load: copy the caller's f64 tables to HBM and derive the f32
+// tile-major operands streamed by the select kernels (knn_depth.cu, knn_tnf.cu).
+//
+// Device layouts (RG_TILE = 32 rows per tile, one row per lane):
+//   tnf_t  float4 [n_tiles][d/4][32]   centred rows x - mean(x)  (kmer_counting.rs:367-377)
+//   cov_t  float4 [n_tiles][s][32]     (mean+eps, max(var+eps,1), ln var', +-1/(sqrt(var')*sqrt2))
+//                                      sign of .w = "mean+eps > eps" (coverage_calculator.rs:600-619)
+// Each tile is one contiguous block so a single TMA bulk copy stages it into shared memory, and
+// for a fixed (j/4 or sample) the 32 lanes read 32 consecutive float4 (conflict-free LDS.128).
+#include "rg_internal.cuh"
+
+__global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n, uint32_t d,
+                                     float *__restrict__ out, float *__restrict__ norm) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const uint64_t rows_padded = (n + RG_TILE - 1) / RG_TILE * RG_TILE;
+    if (row >= rows_padded) return;
+    const uint64_t tile = row / RG_TILE;
+    const uint32_t r = (uint32_t)(row % RG_TILE);
+    double x[8];
+    double sum = 0.0;
+    const int iters = (d + 31) / 32;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        uint32_t j = it * 32 + lane;
+        x[it] = (it < iters && j < d && row < n) ? tnf[row * d + j] : 0.0;
+        sum += x[it];
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const double mu = sum / (double)d;
+    double nn = 0.0;
+    int bad = 0;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        uint32_t j = it * 32 + lane;
+        if (it < iters && j < d) {
+            double c = row < n ? x[it] - mu : 0.0;
+            if (!isfinite(c)) { bad = 1; c = 0.0; }
+            nn += c * c;
+            out[((tile * (d / 4) + j / 4) * RG_TILE + r) * 4 + (j & 3)] = (float)c;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) nn += __shfl_xor_sync(0xffffffffu, nn, o);
+    bad = __any_sync(0xffffffffu, bad);
+    // a row with a non-finite centred value (ln 0 in the CLR, kmer_counting.rs:351) is stored as zeros
+    // with a NaN norm: every distance to it becomes NaN -> 1.0 exactly as :410 does in f64
+    if (lane == 0) norm[row] = bad ? __int_as_float(0x7fc00000) : (float)nn;
+}
+
+__global__ void cov_transform_kernel(const double *__restrict__ cov, uint64_t n, uint32_t s, uint32_t variant,
+                                     float4 *__restrict__ out, uint32_t *__restrict__ err_flag) {
+    const uint64_t rows_padded = (n + RG_TILE - 1) / RG_TILE * RG_TILE;
+    const uint64_t total = rows_padded * s;
+    const double eps = variant == RG_VARIANT_FLIGHT ? 1e-6 : 1e-7;
+    for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (uint64_t)gridDim.x * blockDim.x) {
+        // t enumerates the OUTPUT layout so that stores are coalesced
+        const uint32_t r = (uint32_t)(t % RG_TILE);
+        const uint64_t ts = t / RG_TILE;
+        const uint32_t smp = (uint32_t)(ts % s);
+        const uint64_t row = (ts / s) * RG_TILE + r;
+        double mean = 0.0, var = 0.0;
+        if (row < n) {
+            mean = cov[row * 2 * s + 2 * smp];
+            var = cov[row * 2 * s + 2 * smp + 1];
+            if (!isfinite(mean) || !isfinite(var)) { atomicOr(err_flag, 1u); mean = 0.0; var = 0.0; }
+        }
+        const double m = mean + eps;
+        double v = var + eps;
+        if (v < 1.0) v = 1.0;
+        const double inv = 1.0 / (sqrt(v) * 1.4142135623730951);
+        const bool present = m > eps;
+        out[t] = make_float4((float)m, (float)v, (float)log(v), (float)(present ? inv : -inv));
+    }
+}
+
+extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                               uint32_t s, uint32_t variant) {
+    if (!h) return RG_ERR_INVALID;
+    if (!tnf && !cov) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: both tables are NULL");
+    if (n < 2) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: need at least 2 rows, got %llu", (unsigned long long)n);
+    if (n >= 0xffffffffull) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: n must be < 2^32-1");
+    if (tnf && (d == 0 || d % 4 != 0 || d > 256))
+        return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: d=%u must be a multiple of 4 in (0,256] (TNF has 136 bins)", d);
+    if (cov && (s == 0 || s > 4096)) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: s=%u out of range [1,4096]", s);
+    if (variant > RG_VARIANT_FLIGHT) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: unknown variant %u", variant);
+    RG_CUDA(h, cudaSetDevice(h->device));
+    h->n = 0;
+    h->has_tnf = h->has_cov = false;
+    const uint64_t n_tiles = (n + RG_TILE - 1) / RG_TILE;
+    const uint64_t rows_padded = n_tiles * RG_TILE;
+    RG_TRY(rg_reserve(h, h->err_flag, sizeof(uint32_t)));
+    RG_CUDA(h, cudaMemsetAsync(h->err_flag.p, 0, sizeof(uint32_t), h->stream));
+
+    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    if (tnf) {
+        RG_TRY(rg_reserve(h, h->tnf64, n * d * sizeof(double)));
+        RG_TRY(rg_reserve(h, h->tnf_t, rows_padded * d * sizeof(float)));
+        RG_TRY(rg_reserve(h, h->tnf_norm, rows_padded * sizeof(float)));
+        RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->tm.h2d_bytes += n * d * sizeof(double);
+    }
+    if (cov) {
+        RG_TRY(rg_reserve(h, h->cov64, n * 2 * s * sizeof(double)));
+        RG_TRY(rg_reserve(h, h->cov_t, rows_padded * s * sizeof(float4)));
+        RG_CUDA(h, cudaMemcpyAsync(h->cov64.p, cov, n * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->tm.h2d_bytes += n * 2 * s * sizeof(double);
+    }
+    RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    if (tnf) {
+        const int wpb = 8;
+        tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
+            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p);
+        RG_CUDA(h, cudaGetLastError());
+        h->tm.kernel_launches += 1;
+    }
+    if (cov) {
+        const uint64_t total = rows_padded * s;
+        unsigned blocks = (unsigned)((total + 255) / 256);
+        const unsigned cap = (unsigned)h->sm_count * 32u;
+        if (blocks > cap) blocks = cap;
+        cov_transform_kernel<<<blocks, 256, 0, h->stream>>>((const double *)h->cov64.p, n, s, variant,
+                                                            (float4 *)h->cov_t.p, (uint32_t *)h->err_flag.p);
+        RG_CUDA(h, cudaGetLastError());
+        h->tm.kernel_launches += 1;
+    }
+    RG_CUDA(h, cudaEventRecord(h->ev[2], h->stream));
+    uint32_t flag = 0;
+    RG_CUDA(h, cudaMemcpyAsync(&flag, h->err_flag.p, sizeof(flag), cudaMemcpyDeviceToHost, h->stream));
+    RG_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
+    h->tm.transform_ms = rg_elapsed(h->ev[1], h->ev[2]);
+    if (flag)
+        return rg_fail(h, RG_ERR_INVALID,
+                       "rg_knn_load: coverage table holds a non-finite value (the reference panics in "
+                       "Normal::new, coverage_calculator.rs:639)");
+    h->n = n; h->d = d; h->s = s; h->variant = variant; h->n_tiles = n_tiles;
+    h->has_tnf = tnf != nullptr;
+    h->has_cov = cov != nullptr;
+    return RG_OK;
+}

@@ -1,0 +1,158 @@
+// rg_internal.cuh — handle layout, error plumbing and small device helpers shared by the
+// translation units of librosella_gpu.so (sm_100a only; no CPU fallback anywhere).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/rosella_gpu.h"
+
+#define RG_TILE 32u   // rows per tile of the tile-major device layouts (one row per lane)
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct rg_handle {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    std::string err;
+    rg_timings tm = {};
+
+    // ---- kNN state (rg_knn_load)
+    uint64_t n = 0;
+    uint32_t d = 0, s = 0, variant = 0;
+    uint64_t n_tiles = 0;
+    bool has_tnf = false, has_cov = false;
+    DevBuf tnf64, cov64;      // the caller's f64 tables, kept for the f64 re-evaluation
+    DevBuf tnf_t;             // f32 centred rows, tile-major [tile][d/4][32] float4
+    DevBuf tnf_norm;          // f32 [n_tiles*32] sum of squares of the centred row (NaN = non-finite row)
+    DevBuf cov_t;             // float4 (mean, var, ln var, +-1/(sd*sqrt2)) tile-major [tile][s][32]
+    DevBuf err_flag;          // u32 device error word (non-finite coverage, ...)
+    DevBuf cand_d, cand_i;    // select-phase candidates [rows][kprime]
+    DevBuf out_i, out_d, out_nv; // device staging of final lists for host-output calls
+
+    // ---- TNF counting state
+    uint64_t tnf_n = 0, tnf_words = 0, tnf_bytes = 0;
+    int tnf_mode = 0;         // 0 none, 1 packed resident, 2 ascii resident
+    DevBuf codes, valid, woff, ascii, aoff, counts, nkmers, freqs;
+    DevBuf tnf_tables;        // 256 B little-endian window -> bin LUT, then 256 B byte-class table
+    DevBuf chunk_start;       // u64 [n+1] exclusive scan of chunks per record
+    uint64_t tnf_chunks = 0;
+};
+
+int32_t rg_fail(rg_handle *h, int32_t code, const char *fmt, ...);
+int32_t rg_reserve(rg_handle *h, DevBuf &b, size_t bytes);
+void rg_release(DevBuf &b);
+void rg_set_create_error(const char *msg);
+
+#define RG_CUDA(h, call)                                                                      \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return rg_fail((h), e__ == cudaErrorMemoryAllocation ? RG_ERR_OOM : RG_ERR_CUDA,  \
+                           "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                           __LINE__);                                                         \
+    } while (0)
+
+#define RG_TRY(expr)                 \
+    do {                             \
+        int32_t rc__ = (expr);       \
+        if (rc__ != RG_OK) return rc__; \
+    } while (0)
+
+static inline float rg_elapsed(cudaEvent_t a, cudaEvent_t b) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- mbarrier + TMA bulk copy
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                             uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---------------------------------------------------------------- warp-cooperative top-k list
+// A list of K entries (K a multiple of 32) sorted ascending by (dist, arrival order) lives in
+// shared memory and is owned by one warp.  Candidates arrive in increasing index order, so
+// inserting a tie AFTER the equal entries keeps ties ordered by index.
+template <int K>
+__device__ __forceinline__ float topk_insert(float *ld, uint32_t *li, float d, uint32_t idx, int lane) {
+    constexpr int C = K / 32;
+    float pv[C];
+    uint32_t pi[C];
+    int pos = 0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        int e = c * 32 + lane;
+        float v = ld[e];
+        pos += __popc(__ballot_sync(0xffffffffu, v <= d));
+        pv[c] = e > 0 ? ld[e - 1] : 0.f;
+        pi[c] = e > 0 ? li[e - 1] : 0u;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        int e = c * 32 + lane;
+        if (e == pos) { ld[e] = d; li[e] = idx; }
+        else if (e > pos) { ld[e] = pv[c]; li[e] = pi[c]; }
+    }
+    __syncwarp();
+    return ld[K - 1];
+}
+
+// Offer the per-lane candidates (d, idx) of one warp step to the list; thr is the current K-th
+// distance (warp-uniform).  Lanes are visited in increasing lane (= index) order.
+template <int K>
+__device__ __forceinline__ void topk_offer(float *ld, uint32_t *li, float d, uint32_t idx, float &thr,
+                                           int lane) {
+    unsigned m = __ballot_sync(0xffffffffu, d < thr);
+    while (m) {
+        int src = __ffs(m) - 1;
+        m &= m - 1;
+        float cd = __shfl_sync(0xffffffffu, d, src);
+        uint32_t ci = __shfl_sync(0xffffffffu, idx, src);
+        if (cd < thr) thr = topk_insert<K>(ld, li, cd, ci, lane);
+    }
+}
+#endif  // __CUDACC__

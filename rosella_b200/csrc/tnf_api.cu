@@ -1,0 +1,141 @@
+// tnf_api.cu — C ABI of the TNF path (include/rosella_gpu.h, "TNF counting").
+#include <vector>
+
+#include "rg_internal.cuh"
+#include "tnf_tables.h"
+
+int32_t rg_tnf_launch_packed(rg_handle *h);
+int32_t rg_tnf_launch_ascii(rg_handle *h);
+int32_t rg_tnf_launch_freq(rg_handle *h);
+uint32_t rg_tnf_chunk_words();
+uint32_t rg_tnf_chunk_bytes();
+
+static int32_t ensure_tables(rg_handle *h) {
+    if (h->tnf_tables.p) return RG_OK;
+    uint8_t t[512];
+    rg::build_bin_tables(nullptr, t, nullptr);
+    rg::build_class_table(t + 256);
+    RG_TRY(rg_reserve(h, h->tnf_tables, sizeof(t)));
+    RG_CUDA(h, cudaMemcpy(h->tnf_tables.p, t, sizeof(t), cudaMemcpyHostToDevice));
+    return RG_OK;
+}
+
+// exclusive scan of ceil(len/unit) over records -> device; lens given as an offsets array
+static int32_t upload_chunks(rg_handle *h, const uint64_t *offsets, uint64_t n, uint64_t unit) {
+    std::vector<uint64_t> start(n + 1);
+    start[0] = 0;
+    for (uint64_t r = 0; r < n; ++r) start[r + 1] = start[r] + (offsets[r + 1] - offsets[r] + unit - 1) / unit;
+    h->tnf_chunks = start[n];
+    RG_TRY(rg_reserve(h, h->chunk_start, (n + 1) * sizeof(uint64_t)));
+    RG_CUDA(h, cudaMemcpyAsync(h->chunk_start.p, start.data(), (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaStreamSynchronize(h->stream));   // start[] goes out of scope
+    return RG_OK;
+}
+
+static int32_t reserve_outputs(rg_handle *h, uint64_t n) {
+    RG_TRY(rg_reserve(h, h->counts, n * RG_NBINS * sizeof(uint32_t)));
+    RG_TRY(rg_reserve(h, h->nkmers, n * sizeof(uint64_t)));
+    RG_TRY(rg_reserve(h, h->freqs, n * RG_NBINS * sizeof(double)));
+    return RG_OK;
+}
+
+extern "C" {
+
+int32_t rg_tnf_load_packed(rg_handle *h, const uint64_t *codes, const uint32_t *valid, const uint64_t *word_offsets,
+                           uint64_t n) {
+    if (!h) return RG_ERR_INVALID;
+    if (!word_offsets || (n && (!codes || !valid))) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_load_packed: NULL pointer");
+    RG_CUDA(h, cudaSetDevice(h->device));
+    h->tnf_mode = 0;
+    for (uint64_t r = 0; r < n; ++r)
+        if (word_offsets[r + 1] < word_offsets[r]) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_load_packed: word_offsets must be non-decreasing");
+    const uint64_t words = n ? word_offsets[n] : 0;
+    RG_TRY(ensure_tables(h));
+    RG_TRY(rg_reserve(h, h->codes, words * sizeof(uint64_t)));
+    RG_TRY(rg_reserve(h, h->valid, words * sizeof(uint32_t)));
+    RG_TRY(rg_reserve(h, h->woff, (n + 1) * sizeof(uint64_t)));
+    RG_TRY(reserve_outputs(h, n));
+    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    RG_CUDA(h, cudaMemcpyAsync(h->codes.p, codes, words * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaMemcpyAsync(h->valid.p, valid, words * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaMemcpyAsync(h->woff.p, word_offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    RG_TRY(upload_chunks(h, word_offsets, n, rg_tnf_chunk_words()));
+    h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
+    h->tm.h2d_bytes += words * 12 + (n + 1) * 16;
+    h->tnf_n = n; h->tnf_words = words; h->tnf_bytes = 0; h->tnf_mode = 1;
+    return RG_OK;
+}
+
+int32_t rg_tnf_load_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n) {
+    if (!h) return RG_ERR_INVALID;
+    if (!offsets || (n && !seq && offsets[n] > 0)) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_load_ascii: NULL pointer");
+    RG_CUDA(h, cudaSetDevice(h->device));
+    h->tnf_mode = 0;
+    for (uint64_t r = 0; r < n; ++r)
+        if (offsets[r + 1] < offsets[r]) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_load_ascii: offsets must be non-decreasing");
+    const uint64_t lo = n ? offsets[0] : 0, hi = n ? offsets[n] : 0;
+    RG_TRY(ensure_tables(h));
+    RG_TRY(rg_reserve(h, h->ascii, hi));
+    RG_TRY(rg_reserve(h, h->aoff, (n + 1) * sizeof(uint64_t)));
+    RG_TRY(reserve_outputs(h, n));
+    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    if (hi > lo)
+        RG_CUDA(h, cudaMemcpyAsync((uint8_t *)h->ascii.p + lo, seq + lo, hi - lo, cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaMemcpyAsync(h->aoff.p, offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    RG_TRY(upload_chunks(h, offsets, n, rg_tnf_chunk_bytes()));
+    h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
+    h->tm.h2d_bytes += (hi - lo) + (n + 1) * 16;
+    h->tnf_n = n; h->tnf_words = 0; h->tnf_bytes = hi - lo; h->tnf_mode = 2;
+    return RG_OK;
+}
+
+int32_t rg_tnf_count_resident(rg_handle *h) {
+    if (!h) return RG_ERR_INVALID;
+    if (h->tnf_mode == 0) return rg_fail(h, RG_ERR_STATE, "rg_tnf_count_resident: nothing loaded (rg_tnf_load_* first)");
+    RG_CUDA(h, cudaSetDevice(h->device));
+    RG_CUDA(h, cudaMemsetAsync(h->counts.p, 0, h->tnf_n * RG_NBINS * sizeof(uint32_t), h->stream));
+    RG_CUDA(h, cudaEventRecord(h->ev[6], h->stream));
+    RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed(h) : rg_tnf_launch_ascii(h));
+    RG_CUDA(h, cudaEventRecord(h->ev[7], h->stream));
+    RG_TRY(rg_tnf_launch_freq(h));
+    h->tm.tnf_count_ms = -1.0;   // resolved lazily by rg_get_timings
+    return RG_OK;
+}
+
+int32_t rg_tnf_fetch(rg_handle *h, uint32_t *counts, uint64_t *n_kmers, double *freqs) {
+    if (!h) return RG_ERR_INVALID;
+    if (h->tnf_mode == 0) return rg_fail(h, RG_ERR_STATE, "rg_tnf_fetch: nothing counted");
+    RG_CUDA(h, cudaSetDevice(h->device));
+    const uint64_t n = h->tnf_n;
+    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    if (counts) RG_CUDA(h, cudaMemcpyAsync(counts, h->counts.p, n * RG_NBINS * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (n_kmers) RG_CUDA(h, cudaMemcpyAsync(n_kmers, h->nkmers.p, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    if (freqs) RG_CUDA(h, cudaMemcpyAsync(freqs, h->freqs.p, n * RG_NBINS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    RG_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->tm.d2h_ms = rg_elapsed(h->ev[0], h->ev[1]);
+    h->tm.d2h_bytes += (counts ? n * RG_NBINS * 4 : 0) + (n_kmers ? n * 8 : 0) + (freqs ? n * RG_NBINS * 8 : 0);
+    return RG_OK;
+}
+
+int32_t rg_tnf_count_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t *counts,
+                           uint64_t *n_kmers, double *freqs) {
+    if (!h) return RG_ERR_INVALID;
+    if (!counts || !n_kmers) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_count_ascii: counts / n_kmers is NULL");
+    RG_TRY(rg_tnf_load_ascii(h, seq, offsets, n));
+    RG_TRY(rg_tnf_count_resident(h));
+    return rg_tnf_fetch(h, counts, n_kmers, freqs);
+}
+
+int32_t rg_tnf_count_packed(rg_handle *h, const uint64_t *codes, const uint32_t *valid, const uint64_t *word_offsets,
+                            uint64_t n, uint32_t *counts, uint64_t *n_kmers, double *freqs) {
+    if (!h) return RG_ERR_INVALID;
+    if (!counts || !n_kmers) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_count_packed: counts / n_kmers is NULL");
+    RG_TRY(rg_tnf_load_packed(h, codes, valid, word_offsets, n));
+    RG_TRY(rg_tnf_count_resident(h));
+    return rg_tnf_fetch(h, counts, n_kmers, freqs);
+}
+
+}  // extern "C"

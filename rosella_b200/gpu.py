@@ -1,0 +1,178 @@
+"""Thin Python harness over the C ABI (tests, bench, smoke).  One `Context` = one rg_handle = one GPU.
+All compute happens in librosella_gpu.so; nothing here falls back to the CPU."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import GRAPH_DEPTH, GRAPH_TNF, NBINS, VARIANT_FLIGHT, VARIANT_RUST, RosellaGpuError, Timings
+
+__all__ = ["Context", "canonical_kmers", "pack_host", "GRAPH_TNF", "GRAPH_DEPTH", "VARIANT_RUST", "VARIANT_FLIGHT"]
+
+
+def canonical_kmers() -> list[str]:
+    buf = np.zeros(NBINS * 4, np.uint8)
+    rc = _lib.load().rg_tnf_canonical_kmers(_lib.ptr(buf, C.c_uint8))
+    if rc:
+        raise RosellaGpuError(rc, "rg_tnf_canonical_kmers")
+    return [bytes(buf[4 * i:4 * i + 4]).decode() for i in range(NBINS)]
+
+
+def pack_host(seq: np.ndarray, offsets: np.ndarray, threads: int = 0):
+    """needletail normalize(false) + 2-bit/validity packing on the host -> (codes u64, valid u32, word_offsets u64)."""
+    lib = _lib.load()
+    seq = np.ascontiguousarray(seq, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    n = len(offsets) - 1
+    words = lib.rg_tnf_packed_words(_lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n)
+    codes = np.zeros(max(words, 1), np.uint64)
+    valid = np.zeros(max(words, 1), np.uint32)
+    woff = np.zeros(n + 1, np.uint64)
+    rc = lib.rg_tnf_pack_host(_lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n, _lib.ptr(codes, C.c_uint64),
+                              _lib.ptr(valid, C.c_uint32), _lib.ptr(woff, C.c_uint64), threads)
+    if rc:
+        raise RosellaGpuError(rc, "rg_tnf_pack_host")
+    return codes[:words], valid[:words], woff
+
+
+class Context:
+    def __init__(self, device: int = 0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.rg_create(device, C.byref(h))
+        if rc:
+            raise RosellaGpuError(rc, (self.lib.rg_last_error(None) or b"").decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.rg_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc: int):
+        if rc:
+            raise RosellaGpuError(rc, (self.lib.rg_last_error(self.h) or b"").decode())
+
+    def sync(self):
+        self._chk(self.lib.rg_sync(self.h))
+
+    @property
+    def stream(self) -> int:
+        return self.lib.rg_stream(self.h) or 0
+
+    def timings(self) -> dict:
+        t = Timings()
+        self._chk(self.lib.rg_get_timings(self.h, C.byref(t)))
+        return t.as_dict()
+
+    # ------------------------------------------------------------------ TNF
+    def _tnf_out(self, n):
+        return np.zeros((n, NBINS), np.uint32), np.zeros(n, np.uint64), np.zeros((n, NBINS), np.float64)
+
+    def tnf_count_ascii(self, seq, offsets):
+        seq = np.ascontiguousarray(seq, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        counts, nk, freqs = self._tnf_out(n)
+        self._chk(self.lib.rg_tnf_count_ascii(self.h, _lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n,
+                                              _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
+                                              _lib.ptr(freqs, C.c_double)))
+        return counts, nk, freqs
+
+    def tnf_count_packed(self, codes, valid, word_offsets):
+        codes = np.ascontiguousarray(codes, np.uint64)
+        valid = np.ascontiguousarray(valid, np.uint32)
+        word_offsets = np.ascontiguousarray(word_offsets, np.uint64)
+        n = len(word_offsets) - 1
+        counts, nk, freqs = self._tnf_out(n)
+        self._chk(self.lib.rg_tnf_count_packed(self.h, _lib.ptr(codes, C.c_uint64), _lib.ptr(valid, C.c_uint32),
+                                               _lib.ptr(word_offsets, C.c_uint64), n, _lib.ptr(counts, C.c_uint32),
+                                               _lib.ptr(nk, C.c_uint64), _lib.ptr(freqs, C.c_double)))
+        return counts, nk, freqs
+
+    def tnf_load_packed(self, codes, valid, word_offsets):
+        codes = np.ascontiguousarray(codes, np.uint64)
+        valid = np.ascontiguousarray(valid, np.uint32)
+        word_offsets = np.ascontiguousarray(word_offsets, np.uint64)
+        self._tnf_n = len(word_offsets) - 1
+        self._chk(self.lib.rg_tnf_load_packed(self.h, _lib.ptr(codes, C.c_uint64), _lib.ptr(valid, C.c_uint32),
+                                              _lib.ptr(word_offsets, C.c_uint64), self._tnf_n))
+
+    def tnf_load_ascii(self, seq, offsets):
+        seq = np.ascontiguousarray(seq, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        self._tnf_n = len(offsets) - 1
+        self._chk(self.lib.rg_tnf_load_ascii(self.h, _lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), self._tnf_n))
+
+    def tnf_count_resident(self):
+        self._chk(self.lib.rg_tnf_count_resident(self.h))
+
+    def tnf_fetch(self):
+        counts, nk, freqs = self._tnf_out(self._tnf_n)
+        self._chk(self.lib.rg_tnf_fetch(self.h, _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
+                                        _lib.ptr(freqs, C.c_double)))
+        return counts, nk, freqs
+
+    # ------------------------------------------------------------------ kNN
+    def knn_load(self, tnf, cov, variant: int = VARIANT_RUST):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        n = (tnf if tnf is not None else cov).shape[0]
+        d = tnf.shape[1] if tnf is not None else NBINS
+        s = cov.shape[1] // 2 if cov is not None else 1
+        self._n = n
+        self._chk(self.lib.rg_knn_load(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, variant))
+
+    def knn_search(self, which: int, k: int, q_begin: int = 0, q_end: int | None = None):
+        q_end = self._n if q_end is None else q_end
+        nq = max(q_end - q_begin, 0)
+        idx = np.zeros((nq, k), np.uint32)
+        dist = np.zeros((nq, k), np.float32)
+        nv = np.zeros(nq, np.uint32)
+        self._chk(self.lib.rg_knn_search(self.h, which, k, q_begin, q_end, _lib.ptr(idx, C.c_uint32),
+                                         _lib.ptr(dist, C.c_float), _lib.ptr(nv, C.c_uint32)))
+        return idx, dist, nv
+
+    def knn_search_dev(self, which: int, k: int, q_begin: int, q_end: int, idx_ptr: int, dist_ptr: int,
+                       nvalid_ptr: int = 0):
+        """Outputs are raw device addresses (e.g. torch tensor .data_ptr()); asynchronous on self.stream."""
+        self._chk(self.lib.rg_knn_search_dev(self.h, which, k, q_begin, q_end, idx_ptr, dist_ptr, nvalid_ptr or None))
+
+    def knn_build(self, tnf, cov, k: int, variant: int = VARIANT_RUST, which_mask: int = 3):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        n = (tnf if tnf is not None else cov).shape[0]
+        d = tnf.shape[1] if tnf is not None else NBINS
+        s = cov.shape[1] // 2 if cov is not None else 1
+        ti, td = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        di, dd = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        self._chk(self.lib.rg_knn_build(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, k, variant,
+                                        which_mask, _lib.ptr(ti, C.c_uint32), _lib.ptr(td, C.c_float),
+                                        _lib.ptr(di, C.c_uint32), _lib.ptr(dd, C.c_float)))
+        self._n = n
+        return (ti, td), (di, dd)
+
+    # ------------------------------------------------------------------ graph post-ops
+    def graph_mutual(self, idx, keep_n_edges: int):
+        idx = np.ascontiguousarray(idx, np.uint32)
+        keep = np.zeros(idx.shape, np.uint8)
+        self._chk(self.lib.rg_graph_mutual(self.h, _lib.ptr(idx, C.c_uint32), idx.shape[0], idx.shape[1], keep_n_edges,
+                                           _lib.ptr(keep, C.c_uint8)))
+        return keep
+
+    def graph_intersect(self, base, other, keep_n_edges: int):
+        base = np.ascontiguousarray(base, np.uint32)
+        other = np.ascontiguousarray(other, np.uint32)
+        keep = np.zeros(base.shape, np.uint8)
+        self._chk(self.lib.rg_graph_intersect(self.h, _lib.ptr(base, C.c_uint32), _lib.ptr(other, C.c_uint32),
+                                              base.shape[0], base.shape[1], keep_n_edges, _lib.ptr(keep, C.c_uint8)))
+        return keep

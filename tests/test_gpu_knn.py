@@ -1,0 +1,172 @@
+"""GPU parity: exact kNN graphs through the C ABI vs the exhaustive f64 oracle.
+
+Tolerances (stated per SURVEY §8c).  The library selects K' > k candidates per row in FP32 and then
+re-evaluates them with the reference's f64 arithmetic, truncated to f32 as embedder.rs:125,:170 do:
+  * a reported distance must equal the oracle's f32 distance of that (row, neighbour) pair within
+    TAU_REL = 2.4e-7 relative (2 f32 ulps: device vs glibc erfc/log/exp differ in the last f64 bits,
+    which can straddle an f32 rounding boundary);
+  * every returned neighbour must lie within TAU of the oracle's k-th distance, and the k-th distances
+    must agree within TAU (ties at the boundary may swap);
+  * tie-aware recall must be >= 0.999 (the FP32 select phase may only lose a true neighbour at the
+    K' boundary).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from rosella_b200 import gpu, synth
+
+pytestmark = pytest.mark.gpu
+
+TAU_REL = 2.4e-7
+PAD = 0xFFFFFFFF
+
+
+def _pair_dist(data, which, variant, i, j):
+    if which == oracle.TNF:
+        v = oracle.rho_flight(data[i], data[j]) if variant == oracle.FLIGHT else oracle.kmer_correlation(data[i], data[j])
+        if np.isnan(v):
+            return np.float32(0.0 if variant == oracle.RUST else 2.0)
+    else:
+        v = oracle.metabat(data[i], data[j], variant)
+        if np.isnan(v):
+            return np.float32(1.0)
+    return np.float32(v)
+
+
+def check_against_oracle(data, which, variant, k, idx, dist, q_begin=0, min_recall=0.999):
+    nq = idx.shape[0]
+    qrows = np.arange(q_begin, q_begin + nq, dtype=np.uint64)
+    oidx, odist, _ = oracle.knn(data, which, k, variant, qrows=qrows)
+    tau = lambda x: TAU_REL * np.maximum(np.abs(x), 1e-30)
+    hits = total = 0
+    for r in range(nq):
+        valid = idx[r] != PAD
+        assert valid.sum() == (oidx[r] != PAD).sum()
+        assert (idx[r][valid] != q_begin + r).all()                      # self excluded
+        assert len(set(idx[r][valid].tolist())) == valid.sum()           # no duplicates
+        d = dist[r][valid]
+        assert (np.diff(d) >= 0).all()                                   # ascending
+        same = idx[r] == oidx[r]
+        assert np.all(np.abs(dist[r][same & valid] - odist[r][same & valid]) <= tau(odist[r][same & valid]))
+        kth = odist[r][valid][-1] if valid.any() else 0.0
+        for p in np.where(valid & ~same)[0]:
+            od = _pair_dist(data, which, variant, q_begin + r, int(idx[r][p]))
+            assert abs(od - dist[r][p]) <= tau(od), (r, p, od, dist[r][p])
+            assert od <= kth + tau(kth), (r, p, od, kth)
+        if valid.any():
+            assert abs(d[-1] - kth) <= tau(kth)
+        # tie-aware recall: an oracle neighbour counts as found if present, or if its distance ties the k-th
+        got = set(idx[r][valid].tolist())
+        for p in np.where(oidx[r] != PAD)[0]:
+            total += 1
+            hits += (int(oidx[r][p]) in got) or (odist[r][p] >= kth - tau(kth))
+    recall = hits / max(total, 1)
+    assert recall >= min_recall, recall
+    exact = float((idx == oidx).mean())
+    return recall, exact
+
+
+@pytest.mark.parametrize("variant", [gpu.VARIANT_RUST, gpu.VARIANT_FLIGHT])
+def test_knn_synthetic_3000(ctx, variant):
+    tnf, cov, _ = synth.knn_tables(3000, 10, flight=variant == gpu.VARIANT_FLIGHT)
+    (ti, td), (di, dd) = ctx.knn_build(tnf, cov, 30, variant)
+    r1, e1 = check_against_oracle(tnf, oracle.TNF, variant, 30, ti, td)
+    r2, e2 = check_against_oracle(cov, oracle.DEPTH, variant, 30, di, dd)
+    print(f"variant {variant}: tnf recall {r1:.5f} exact-position {e1:.5f}; depth recall {r2:.5f} exact-position {e2:.5f}")
+    assert e1 > 0.99 and e2 > 0.98
+
+
+def test_knn_sharded_query_ranges(ctx):
+    """Rank shards [q_begin, q_end) that are not tile aligned concatenate to the full result."""
+    tnf, cov, _ = synth.knn_tables(1500, 5, seed=11)
+    ctx.knn_load(tnf, cov, gpu.VARIANT_RUST)
+    full_i, full_d, nv = ctx.knn_search(gpu.GRAPH_DEPTH, 10)
+    assert (nv == 10).all()
+    parts = [ctx.knn_search(gpu.GRAPH_DEPTH, 10, b, e) for b, e in [(0, 37), (37, 1000), (1000, 1500)]]
+    assert np.array_equal(np.concatenate([p[0] for p in parts]), full_i)
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), full_d)
+    check_against_oracle(cov, oracle.DEPTH, oracle.RUST, 10, parts[1][0][:200], parts[1][1][:200], q_begin=37)
+    ti, td, _ = ctx.knn_search(gpu.GRAPH_TNF, 10, 777, 901)
+    check_against_oracle(tnf, oracle.TNF, oracle.RUST, 10, ti, td, q_begin=777)
+    e_i, e_d, _ = ctx.knn_search(gpu.GRAPH_TNF, 10, 5, 5)
+    assert e_i.shape == (0, 10)
+
+
+@pytest.mark.parametrize("k,n", [(1, 300), (48, 400), (100, 700), (200, 600)])
+def test_knn_k_range(ctx, k, n):
+    tnf, cov, _ = synth.knn_tables(n, 3, seed=5 + k)
+    (ti, td), (di, dd) = ctx.knn_build(tnf, cov, k)
+    check_against_oracle(tnf, oracle.TNF, oracle.RUST, k, ti, td)
+    check_against_oracle(cov, oracle.DEPTH, oracle.RUST, k, di, dd)
+
+
+def test_knn_fewer_rows_than_k(ctx):
+    tnf, cov, _ = synth.knn_tables(10, 2, seed=3)
+    (ti, td), (di, dd) = ctx.knn_build(tnf, cov, 30)
+    assert (ti[:, 9:] == PAD).all() and np.isinf(td[:, 9:]).all() and (ti[:, :9] != PAD).all()
+    check_against_oracle(tnf, oracle.TNF, oracle.RUST, 30, ti, td)
+    check_against_oracle(cov, oracle.DEPTH, oracle.RUST, 30, di, dd)
+
+
+def test_knn_degenerate_rows(ctx):
+    """Duplicates, all-zero coverage, constant TNF rows, a TNF row holding -inf (ln 0 in the CLR)."""
+    tnf, cov, _ = synth.knn_tables(400, 4, seed=9)
+    tnf[5] = tnf[4]; cov[5] = cov[4]            # duplicate contig
+    cov[7] = 0.0                                 # absent everywhere
+    cov[8, 1::2] = 0.0                           # zero variance
+    tnf[9] = 0.0; tnf[10] = 0.0                  # constant rows: both norms 0 -> distance 0 between them
+    tnf[11, 3] = -np.inf                         # flagged row: distance 1 to everything
+    cov[12] = cov[13] * 1.0000001               # nearly identical coverage
+    for variant in (gpu.VARIANT_RUST, gpu.VARIANT_FLIGHT):
+        (ti, td), (di, dd) = ctx.knn_build(tnf, cov, 30, variant)
+        check_against_oracle(tnf, oracle.TNF, variant, 30, ti, td)
+        check_against_oracle(cov, oracle.DEPTH, variant, 30, di, dd, min_recall=0.995)
+    (ti, td), _ = ctx.knn_build(tnf, cov, 30, gpu.VARIANT_RUST)
+    assert ti[9, 0] == 10 and td[9, 0] == 0.0 and ti[4, 0] == 5
+    assert (td[11] == 1.0).all() and list(ti[11]) == list(range(11)) + list(range(12, 31))   # ties by index
+
+
+def test_flight_golden_vectors_through_the_gpu(ctx, golden_dir):
+    """All-neighbour lists (k = n-1) reproduce the reference's own numba outputs."""
+    g = np.load(os.path.join(golden_dir, "flight_metrics.npz"))
+    for s in (1, 3, 10):
+        cov, ref = g[f"cov_s{s}"], g[f"metabat_nn_s{s}"]
+        n = len(cov)
+        ctx.knn_load(None, cov, gpu.VARIANT_FLIGHT)
+        idx, dist, _ = ctx.knn_search(gpu.GRAPH_DEPTH, n - 1)
+        for i in range(n):
+            want = ref[i][idx[i]].astype(np.float32)
+            assert np.all(np.abs(dist[i] - want) <= TAU_REL * np.abs(want)), (s, i)
+    x, ref = g["tnf_clr"], g["rho"]
+    ctx.knn_load(x, None, gpu.VARIANT_FLIGHT)
+    idx, dist, _ = ctx.knn_search(gpu.GRAPH_TNF, len(x) - 1)
+    for i in range(len(x)):
+        want = ref[i][idx[i]].astype(np.float32)
+        assert np.all(np.abs(dist[i] - want) <= TAU_REL * np.abs(want) + 1e-12)
+
+
+def test_errors(ctx):
+    tnf, cov, _ = synth.knn_tables(64, 2, seed=1)
+    bad = cov.copy(); bad[3, 1] = np.nan
+    with pytest.raises(gpu.RosellaGpuError, match="non-finite"):
+        ctx.knn_load(tnf, bad)
+    with pytest.raises(gpu.RosellaGpuError, match="no tables loaded"):
+        ctx.knn_search(gpu.GRAPH_TNF, 5, 0, 10)
+    ctx.knn_load(tnf, None)
+    with pytest.raises(gpu.RosellaGpuError, match="no coverage table"):
+        ctx.knn_search(gpu.GRAPH_DEPTH, 5, 0, 10)
+    with pytest.raises(gpu.RosellaGpuError, match="k=0"):
+        ctx.knn_search(gpu.GRAPH_TNF, 0, 0, 10)
+    with pytest.raises(gpu.RosellaGpuError, match="outside"):
+        ctx.knn_search(gpu.GRAPH_TNF, 5, 0, 65)
+
+
+def test_graph_ops(ctx):
+    tnf, cov, _ = synth.knn_tables(500, 3, seed=2)
+    (ti, _), (di, _) = ctx.knn_build(tnf, cov, 12)
+    for keep_n in (0, 5, 12):
+        assert np.array_equal(ctx.graph_mutual(di, keep_n), oracle.mutual_knn(di, keep_n))
+        assert np.array_equal(ctx.graph_intersect(di, ti, keep_n), oracle.intersect(di, ti, keep_n))

@@ -1,0 +1,84 @@
+"""CPU tests of the host side: the C-ABI library loads and exports what include/rosella_gpu.h
+declares, the host packer and canonical index agree with the oracle, and GPU entry points fail
+loudly (no CPU fallback) when no device is present."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from rosella_b200 import _lib, gpu, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "rosella_gpu.h")).read()
+    declared = set(re.findall(r"\b(rg_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"rg_handle"}
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    lib = _lib.load()
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert lib.rg_abi_version() == 1
+
+
+def test_canonical_kmers_match_oracle():
+    assert gpu.canonical_kmers() == oracle.canonical_kmers()
+
+
+def _unpack(codes, valid, woff, rec):
+    out = []
+    for w in range(int(woff[rec]), int(woff[rec + 1])):
+        for j in range(32):
+            if (int(valid[w]) >> j) & 1:
+                out.append("ACGT"[(int(codes[w]) >> (2 * j)) & 3])
+            else:
+                out.append("x")
+    return "".join(out)
+
+
+def test_pack_host_follows_needletail_normalize(golden_dir):
+    g = np.load(os.path.join(golden_dir, "tnf_fixtures.npz"))
+    seq, offsets = g["seq"], g["offsets"]
+    codes, valid, woff = gpu.pack_host(seq, offsets, threads=3)
+    assert len(woff) == len(offsets) and woff[-1] == len(codes) == len(valid)
+    for rec in list(range(12)) + list(range(len(offsets) - 10, len(offsets) - 1)):
+        raw = bytes(seq[int(offsets[rec]):int(offsets[rec + 1])])
+        norm = oracle.normalize(raw).decode()
+        want = "".join(c if c in "ACGT" else "x" for c in norm)
+        got = _unpack(codes, valid, woff, rec)
+        assert got[:len(want)] == want
+        assert set(got[len(want):]) <= {"x"} and len(got) - len(want) < 32
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    lib = _lib.load()
+    h = C.c_void_p()
+    rc = lib.rg_create(0, C.byref(h))
+    assert rc == -1 and not h.value                       # RG_ERR_NO_DEVICE
+    assert b"no CPU fallback" in lib.rg_last_error(None)
+    with pytest.raises(gpu.RosellaGpuError):
+        gpu.Context(0)
+
+
+def test_synth_shapes_and_determinism():
+    tnf, cov, genome = synth.knn_tables(500, 4)
+    tnf2, cov2, _ = synth.knn_tables(500, 4)
+    assert tnf.shape == (500, 136) and cov.shape == (500, 8)
+    assert np.array_equal(tnf, tnf2) and np.array_equal(cov, cov2)
+    assert np.isfinite(tnf).all() and (cov >= 0).all()
+    assert np.allclose(np.exp(tnf).mean(axis=1) * 0 + tnf.shape[1], 136)
+    seq, offs = synth.contigs(200_000, threads=2)
+    seq2, offs2 = synth.contigs(200_000, threads=1)
+    assert np.array_equal(seq, seq2) and np.array_equal(offs, offs2)
+    assert offs[-1] == len(seq) >= 200_000
+    wrapped, woffs = synth.fasta_wrap(seq, offs)
+    c1, n1, _ = oracle.tnf_count(seq, offs, fast=True)
+    c2, n2, _ = oracle.tnf_count(wrapped, woffs, fast=True)
+    assert np.array_equal(c1, c2) and np.array_equal(n1, n2)

@@ -1,0 +1,123 @@
+"""CPU tests: the oracle against the golden vectors (tests/golden/, generated from the reference by
+oracle/make_golden.py) and against the known-answer values of SURVEY.md §4."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+
+@pytest.fixture(scope="module")
+def tnf_fix(golden_dir):
+    return np.load(os.path.join(golden_dir, "tnf_fixtures.npz"))
+
+
+@pytest.fixture(scope="module")
+def flight(golden_dir):
+    return np.load(os.path.join(golden_dir, "flight_metrics.npz"))
+
+
+def test_canonical_kmers_known_answers(tnf_fix):
+    names = oracle.canonical_kmers()
+    assert len(names) == 136 and len(set(names)) == 136
+    assert names[:12] == ["AAAA", "AAAC", "AAAG", "AAAT", "AACA", "AACC", "AACG", "AACT", "AAGA", "AAGC", "AAGG", "AAGT"]
+    assert names[-6:] == ["TCAA", "TCCA", "TCGA", "TGAA", "TGCA", "TTAA"]
+    comp = str.maketrans("ACGT", "TGCA")
+    assert sum(1 for k in names if k == k[::-1].translate(comp)) == 16     # palindromes
+    assert names == list(tnf_fix["canonical"])
+    lut = oracle.code_to_bin()
+    assert lut.max() == 135 and len(np.unique(lut)) == 136
+
+
+def test_tnf_counts_match_reference_model(tnf_fix):
+    for fast in (False, True):
+        counts, nk, freqs = oracle.tnf_count(tnf_fix["seq"], tnf_fix["offsets"], fast=fast)
+        assert np.array_equal(counts, tnf_fix["counts"])
+        assert np.array_equal(nk, tnf_fix["n_kmers"])
+    # SURVEY §4 known answers on tests/data/ben/random10000.fna
+    assert nk[0] == 9997 and list(counts[0, :6]) == [88, 87, 65, 71, 89, 104]
+    assert counts[0].max() == 104 and counts[0].min() == 27
+    assert nk[1] == 1997 and list(counts[1, :6]) == [17, 12, 13, 25, 15, 15]
+    assert all(nk[2:11] == 4)
+    # 0/0 -> NaN row, as kmer_counting.rs:104-107
+    empty = np.where(nk == 0)[0]
+    assert len(empty) >= 3 and np.isnan(freqs[empty]).all()
+    ok = nk > 0
+    assert np.allclose(freqs[ok].sum(axis=1), 1.0)
+
+
+def test_normalize_semantics():
+    assert oracle.normalize(b"acgtnACGTN-") == b"ACGTNACGTN-"
+    assert oracle.normalize(b"uU.~ \t\r\nRYKMbdhv*") == b"TT--NNNNNNNNN"
+
+
+@pytest.mark.parametrize("s", [1, 3, 10])
+def test_metabat_flight_variant_is_pinned(flight, s):
+    cov = flight[f"cov_s{s}"]
+    ref = flight[f"metabat_nn_s{s}"]
+    got = np.array([[oracle.metabat(a, b, oracle.FLIGHT) for b in cov] for a in cov])
+    # numba compiles the reference with fastmath; 1e-12 relative is far below any f32 effect
+    assert np.allclose(got, ref, rtol=1e-12, atol=0)
+    # coverage_distance = same metric except identical rows -> 0 (metrics.py:429-431)
+    cd = flight[f"coverage_distance_s{s}"]
+    same = np.array([[np.array_equal(a, b) for b in cov] for a in cov])
+    assert np.allclose(got[~same], cd[~same], rtol=1e-12, atol=0)
+    assert (cd[same] == 0).all()
+
+
+def test_rho_and_euclid_pinned(flight):
+    x = flight["tnf_clr"]
+    rho = np.array([[oracle.rho_flight(a, b) for b in x] for a in x])
+    eu = np.array([[oracle.tnf_euclidean(a, b) for b in x] for a in x])
+    off = ~np.eye(len(x), dtype=bool)
+    assert np.allclose(rho[off], flight["rho"][off], rtol=1e-12, atol=1e-15)
+    assert np.allclose(eu, flight["tnf_euclidean"], rtol=1e-12, atol=1e-13)
+    # Rust proportionality distance is exactly half of flight's rho
+    kc = np.array([[oracle.kmer_correlation(a, b) for b in x] for a in x])
+    assert np.allclose(2 * kc[off], flight["rho"][off], rtol=1e-12, atol=1e-15)
+
+
+def test_rust_variant_semantics(flight):
+    cov = flight["cov_s3"]
+    d = np.array([[oracle.metabat(a, b, oracle.RUST) for b in cov] for a in cov])
+    assert ((d >= 0) & (d <= 1)).all() and not np.isnan(d).any()
+    assert d[0, 1] == 1.0 and d[6, 6] == 1.0          # identical rows: no contributing sample (:665)
+    # equal-variance branch keeps the sign (:647): a negative d makes the pair NaN -> 1.0, so the
+    # Rust metric is not symmetric
+    assert (d != d.T).any()
+    a = np.array([5.0, 0.5]); b = np.array([9.0, 0.25])       # both variances clamp to 1
+    assert oracle.metabat(a, b, oracle.RUST) < 1.0 and oracle.metabat(b, a, oracle.RUST) == 1.0
+
+
+def test_kmer_correlation_guards():
+    z = np.zeros(136); c = np.ones(136); r = np.random.default_rng(0).normal(size=136)
+    assert oracle.kmer_correlation(z, c) == 0.0           # both centred norms are 0 (:383)
+    assert oracle.kmer_correlation(z, r) == 1.0           # dot == 0 (:385)
+    bad = r.copy(); bad[3] = -np.inf
+    assert oracle.kmer_correlation(bad, r) == 1.0         # NaN -> 1 (:410)
+    assert abs(oracle.kmer_correlation(r, r)) < 1e-15
+
+
+def test_exhaustive_knn_matches_bruteforce():
+    rng = np.random.default_rng(7)
+    x = rng.normal(size=(60, 136))
+    idx, dist, d64 = oracle.knn(x, oracle.TNF, 5)
+    full = np.array([[oracle.kmer_correlation(a, b) for b in x] for a in x]).astype(np.float32)
+    np.fill_diagonal(full, np.inf)
+    for i in range(60):
+        order = np.lexsort((np.arange(60), full[i]))[:5]
+        assert list(order) == list(idx[i])
+        assert np.array_equal(full[i][order], dist[i])
+    # fewer candidates than k: padding
+    idx, dist, _ = oracle.knn(x[:3], oracle.TNF, 5)
+    assert (idx[:, 2:] == 0xFFFFFFFF).all() and np.isinf(dist[:, 2:]).all()
+
+
+def test_graph_ops():
+    idx = np.array([[1, 2], [0, 2], [1, 0xFFFFFFFF]], np.uint32)
+    keep = oracle.mutual_knn(idx, 0)
+    assert keep.tolist() == [[1, 0], [1, 1], [1, 0]]
+    assert oracle.mutual_knn(idx, 1).tolist() == [[1, 0], [1, 1], [1, 0]]
+    other = np.array([[2, 1], [2, 0xFFFFFFFF], [0, 1]], np.uint32)
+    assert oracle.intersect(idx, other, 0).tolist() == [[0, 1], [1, 1], [1, 0]]
