@@ -29,7 +29,7 @@ __device__ __forceinline__ float mufu_rcp(float x) { float y; asm("rcp.approx.ft
 __device__ __forceinline__ float mufu_sqrt(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // erf(x) = sign(x) * (1 - 2^(-t*g(t))), t = min(|x|, 4); g = degree-6 fit of -log2(erfc(t))/t on [0,4],
-// max abs error 1.6e-7 in FP32 (oracle/fit_erf.py).  6 FFMA + 1 FMUL + 1 MUFU.EX2 + 1 FADD.
+// max abs error 1.6e-7 in FP32 (rosella_b200/tools/fit_erf.py).  6 FFMA + 1 FMUL + 1 MUFU.EX2 + 1 FADD.
 __device__ __forceinline__ float erf_fast(float x) {
     const float t = fminf(fabsf(x), 4.0f);
     float p = -1.0021986768753148e-04f;
