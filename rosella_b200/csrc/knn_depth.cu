@@ -19,6 +19,8 @@
 //   narrower distribution is needed because |.| absorbs both sign flips (coverage_calculator.rs:630-651).
 //   Equal-variance branch (:620-623): d = 1/2 (+-)(erf(D*ia/2) + erf(D*ib/2)), sign from :638 (RUST keeps the
 //   sign, so ln of a negative d turns the whole pair into NaN -> 1.0, :659-661).
+#include <cstdlib>
+
 #include "rg_internal.cuh"
 
 namespace {
@@ -204,8 +206,13 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 
 }  // namespace
 
-// cand_d / cand_i must hold q_count * kprime entries
+int32_t rg_launch_depth_select_v2(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
+
+// cand_d / cand_i must hold q_count * kprime entries.  The packed f32x2 kernel (knn_depth2.cu) is the
+// product path; RG_DEPTH_IMPL=1 selects the scalar first-generation kernel for A/B measurements.
 int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    static const bool use_v1 = [] { const char *e = getenv("RG_DEPTH_IMPL"); return e && e[0] == '1'; }();
+    if (!use_v1) return rg_launch_depth_select_v2(h, kprime, q_begin, q_count);
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);
 }

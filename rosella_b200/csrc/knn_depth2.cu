@@ -1,0 +1,228 @@
+// knn_depth2.cu — K2a, second generation: the coverage ("depth") select kernel with the FP32 work
+// of TWO query rows packed into f32x2 instructions (pk.cuh).  Same metric, mapping, shared-memory
+// ring and top-K' lists as knn_depth.cu (read its header first); what changes is the issue cost:
+//   measured on B200 (profiles/r1_microbench_issue_model.json): FFMA 1 cycle/warp, FFMA2 2 cycles
+//   for twice the work, every ALU-pipe op (FSEL, FSETP, FMNMX, LOP3) 2 cycles, MUFU 8 cycles of the
+//   XU pipe.  v1 spent 57 FMA + 19 ALU + 7 MUFU instructions per (pair, sample); here
+//     - the FMA-pipe work is issued as f32x2 (half the issue slots),
+//     - the erf polynomial needs no clamp: degree 7 with a positive leading coefficient, so
+//       t*g(t) grows monotonically past the fitted range and 2^-(t g) underflows to 0 (4 FMNMX gone),
+//     - the equal-variance branch is blended arithmetically (r = 0 and a signed half-difference
+//       he select it) instead of four FSELs, sqrt takes |q| as a source modifier, and the
+//       accumulators are updated by predicated FADDs instead of FSEL + FADD.
+#include "pk.cuh"
+#include "rg_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ float mufu_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float mufu_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float mufu_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float mufu_sqrt(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// erf for both halves: sign(x) * (1 - 2^(-t g(t))), t = |x| (no clamp), g = degree-4 fit of
+// -log2(erfc(t))/t on [0,4] with a positive leading coefficient: max abs error 6.7e-7 in FP32, t g(t)
+// increases monotonically beyond 4 so the result saturates to exactly +-1 (tools/fit_erf.py).
+// 4 FFMA2 + FMUL2 + FADD2 per two values, 2 MUFU.EX2, 2 LOP3.  The error budget is set by the K' - k
+// candidate margin, not by the reported distances (those are re-evaluated in f64).
+__device__ __forceinline__ pk erf2(pk x) {
+    const pk t = abs2(x);
+    pk p = bc(2.944113406715287e-03f);
+    p = fma2(p, t, bc(-2.9589898317605317e-02f));
+    p = fma2(p, t, bc(1.4866547752377543e-01f));
+    p = fma2(p, t, bc(9.185094237957379e-01f));
+    p = fma2(p, t, bc(1.6278889993946153f));
+    const pk y = p * t;
+    const pk r = bc(1.0f) - mk(mufu_ex2(-lo(y)), mufu_ex2(-hi(y)));
+    return mk(copysignf(lo(r), lo(x)), copysignf(hi(r), hi(x)));
+}
+
+// two query rows (halves of ax..aw) against one reference row b, one sample
+template <int VARIANT>
+__device__ __forceinline__ void depth_sample2(const pk ax, const pk ay, const pk az, const pk aw, const float4 b,
+                                              float &acc0, float &cnt0, float &acc1, float &cnt1) {
+    const float ib = fabsf(b.w);
+    const pk ia = abs2(aw);
+    const pk D = ax - bc(b.x);
+    // everything is written in ndv = var_b - var_a = -dv: r = 1/ndv flips the sign of all four erf
+    // arguments, hence of val, which |.| absorbs; ndv is +0 for equal variances, so its sign bit is
+    // exactly "var_a > var_b" (:638) and no separate difference is needed for the RUST sign below
+    const pk ndv = bc(b.y) - ay;
+    const pk t = fma2(ndv, bc(b.z) - az, D * D);
+    const pk q = (ay * bc(b.y)) * t;                                    // :625
+    const pk tmp = mk(mufu_sqrt(fabsf(lo(q))), mufu_sqrt(fabsf(hi(q))));
+    const bool eq0 = fabsf(lo(ndv)) < 1e-4f, eq1 = fabsf(hi(ndv)) < 1e-4f; // :620
+    const pk r = mk(eq0 ? 0.f : mufu_rcp(lo(ndv)), eq1 ? 0.f : mufu_rcp(hi(ndv)));
+    // equal-variance branch: he = +-D/2 (0 otherwise); RUST folds the sign of p1.cdf - p2.cdf (:638,:647)
+    // into it: + when var_a > var_b, - otherwise
+    const pk hD = D * bc(0.5f);
+    float h0 = lo(hD), h1 = hi(hD);
+    if (VARIANT == RG_VARIANT_RUST) {
+        h0 = __uint_as_float(__float_as_uint(h0) ^ (~__float_as_uint(lo(ndv)) & 0x80000000u));
+        h1 = __uint_as_float(__float_as_uint(h1) ^ (~__float_as_uint(hi(ndv)) & 0x80000000u));
+    }
+    const pk he = mk(eq0 ? h0 : 0.f, eq1 ? h1 : 0.f);
+    const pk ra = r * ia, rb = r * bc(ib);
+    const pk A = ay * D, B = bc(b.y) * D;
+    const pk x1 = fma2(tmp - A, ra, he * ia);
+    const pk x2 = neg(tmp + A) * ra;
+    const pk x3 = fma2(tmp - B, rb, neg(he * bc(ib)));
+    const pk x4 = neg(tmp + B) * rb;
+    const pk val = (erf2(x1) - erf2(x2)) - (erf2(x3) - erf2(x4));
+    float v0 = lo(val), v1 = hi(val);
+    if (VARIANT == RG_VARIANT_RUST) {
+        v0 = eq0 ? v0 : fabsf(v0);                                       // :650 |.| ; :647 keeps the sign
+        v1 = eq1 ? v1 : fabsf(v1);
+    } else {
+        v0 = fminf(fmaxf(fabsf(v0), 2e-6f), 2.0f - 2e-6f);              // metrics.py:519,:523 on d = val/2
+        v1 = fminf(fmaxf(fabsf(v1), 2e-6f), 2.0f - 2e-6f);
+    }
+    // :619  (a_mean > EPS || b_mean > EPS) && a_mean != b_mean.  Two absent samples both hold exactly
+    // mean + EPS = EPS, so they are already excluded by the inequality; a present sample has mean + EPS > EPS.
+    // The presence flag carried in the sign of .w is therefore not needed here.
+    const bool c0 = lo(ax) != b.x, c1 = hi(ax) != b.x;
+    const float l0 = mufu_lg2(v0), l1 = mufu_lg2(v1);                    // NaN for v < 0, -inf for 0
+    if (c0) { acc0 += l0; cnt0 += 1.0f; }                                // compiled to predicated FADDs
+    if (c1) { acc1 += l1; cnt1 += 1.0f; }
+}
+
+template <int VARIANT>
+__device__ __forceinline__ float depth_finish(float acc, float cnt) {
+    float d = 0.5f * mufu_ex2(__fdividef(acc, cnt));                     // :656-663
+    if (!(cnt > 0.f)) d = 1.0f;                                          // :665
+    if (d != d) d = 1.0f;                                                // :660, embedder.rs:166
+    return d;
+}
+
+constexpr int QPW = 4;          // query rows per warp = 2 packed pairs
+constexpr int WARPS = 8;
+constexpr int QB = QPW * WARPS; // 32 query rows per CTA
+constexpr int PAIRS = QB / 2;
+
+// Shared memory: 2 reference stages [S][32] float4 | query pairs [S][PAIRS] 2 x float4
+// ({x0,x1,y0,y1},{z0,z1,w0,w1}) | K' lists | 2 mbarriers
+template <int VARIANT, int K>
+__global__ void __launch_bounds__(WARPS * 32, 2)
+depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, uint32_t n_tiles, uint32_t q_begin,
+                     uint32_t q_count, float *__restrict__ cand_d, uint32_t *__restrict__ cand_i) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t tile_f4 = S * RG_TILE;
+    float4 *stage[2] = {reinterpret_cast<float4 *>(smem), reinterpret_cast<float4 *>(smem) + tile_f4};
+    float *qd = reinterpret_cast<float *>(stage[1] + tile_f4);
+    float *list_d = qd + tile_f4 * 4;
+    uint32_t *list_i = reinterpret_cast<uint32_t *>(list_d + QB * K);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(list_i + QB * K);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t q0 = q_begin + blockIdx.x * QB;
+    const uint32_t q_end = q_begin + q_count;
+
+    for (uint32_t i = tid; i < tile_f4; i += WARPS * 32) {
+        const uint32_t s = i / RG_TILE, r = i % RG_TILE;
+        const uint32_t row = min(q0 + r, n - 1);
+        const float4 v = cov_t[((uint64_t)(row / RG_TILE) * S + s) * RG_TILE + row % RG_TILE];
+        float *dst = qd + ((s * PAIRS + (r >> 1)) * 8) + (r & 1);
+        dst[0] = v.x; dst[2] = v.y; dst[4] = v.z; dst[6] = v.w;
+    }
+    for (uint32_t i = tid; i < QB * K; i += WARPS * 32) {
+        list_d[i] = INFINITY;
+        list_i[i] = 0xffffffffu;
+    }
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const uint32_t tile_bytes = tile_f4 * sizeof(float4);
+    if (tid == 0) {
+        mbar_expect_tx(&bars[0], tile_bytes);
+        tma_bulk_g2s(stage[0], cov_t, tile_bytes, &bars[0]);
+    }
+    float thr[QPW];
+    uint32_t qrow[QPW];
+#pragma unroll
+    for (int u = 0; u < QPW; ++u) {
+        thr[u] = INFINITY;
+        qrow[u] = q0 + warp * QPW + u;
+    }
+    const ulonglong2 *qp = reinterpret_cast<const ulonglong2 *>(qd) + warp * 4;   // 2 pairs x 2 ulonglong2
+
+    for (uint32_t t = 0; t < n_tiles; ++t) {
+        __syncthreads();   // every warp is done with tile t-1, so its stage may be overwritten
+        if (tid == 0 && t + 1 < n_tiles) {
+            uint64_t *bar = &bars[(t + 1) & 1];
+            mbar_expect_tx(bar, tile_bytes);
+            tma_bulk_g2s(stage[(t + 1) & 1], cov_t + (uint64_t)(t + 1) * tile_f4, tile_bytes, bar);
+        }
+        mbar_wait(&bars[t & 1], (t >> 1) & 1);
+        const float4 *ref = stage[t & 1];
+        float acc[QPW], cnt[QPW];
+#pragma unroll
+        for (int u = 0; u < QPW; ++u) acc[u] = cnt[u] = 0.f;
+#pragma unroll 2
+        for (uint32_t s = 0; s < S; ++s) {
+            const float4 b = ref[s * RG_TILE + lane];
+#pragma unroll
+            for (int pr = 0; pr < 2; ++pr) {
+                const ulonglong2 xy = qp[s * (PAIRS * 2) + pr * 2], zw = qp[s * (PAIRS * 2) + pr * 2 + 1];
+                depth_sample2<VARIANT>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc[2 * pr], cnt[2 * pr],
+                                       acc[2 * pr + 1], cnt[2 * pr + 1]);
+            }
+        }
+        const uint32_t ridx = t * RG_TILE + lane;
+#pragma unroll
+        for (int u = 0; u < QPW; ++u) {
+            float d = depth_finish<VARIANT>(acc[u], cnt[u]);
+            if (ridx >= n || ridx == qrow[u] || qrow[u] >= q_end) d = INFINITY;
+            topk_offer<K>(list_d + (warp * QPW + u) * K, list_i + (warp * QPW + u) * K, d, ridx, thr[u], lane);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < QPW; ++u) {
+        if (qrow[u] < q_end) {
+            const uint64_t o = (uint64_t)(qrow[u] - q_begin) * K;
+            for (int e = lane; e < K; e += 32) {
+                cand_d[o + e] = list_d[(warp * QPW + u) * K + e];
+                cand_i[o + e] = list_i[(warp * QPW + u) * K + e];
+            }
+        }
+    }
+}
+
+template <int VARIANT, int K>
+int32_t launch(rg_handle *h, uint64_t q_begin, uint64_t q_count) {
+    const size_t tile_bytes = (size_t)h->s * RG_TILE * sizeof(float4);
+    const size_t smem = 3 * tile_bytes + (size_t)QB * K * 8 + 2 * sizeof(uint64_t);
+    if (smem > 227 * 1024)
+        return rg_fail(h, RG_ERR_INVALID,
+                       "depth select: %u samples with K'=%d need %zu bytes of shared memory (> 227 KB); "
+                       "at most ~128 samples are supported in this version", h->s, K, smem);
+    auto kern = depth_select2_kernel<VARIANT, K>;
+    RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)((q_count + QB - 1) / QB);
+    kern<<<grid, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, (uint32_t)h->n, h->s,
+                                                (uint32_t)h->n_tiles, (uint32_t)q_begin, (uint32_t)q_count,
+                                                (float *)h->cand_d.p, (uint32_t *)h->cand_i.p);
+    RG_CUDA(h, cudaGetLastError());
+    h->tm.kernel_launches += 1;
+    return RG_OK;
+}
+
+template <int VARIANT>
+int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    switch (kprime) {
+        case 64: return launch<VARIANT, 64>(h, q_begin, q_count);
+        case 128: return launch<VARIANT, 128>(h, q_begin, q_count);
+        case 256: return launch<VARIANT, 256>(h, q_begin, q_count);
+    }
+    return rg_fail(h, RG_ERR_INVALID, "depth select: unsupported K'=%u", kprime);
+}
+
+}  // namespace
+
+int32_t rg_launch_depth_select_v2(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
+                                           : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);
+}
