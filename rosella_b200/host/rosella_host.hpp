@@ -1,0 +1,139 @@
+// rosella_host.hpp — C++17 host-side mirror of the reference's Rust interface for the hot path, on top
+// of the C ABI (include/rosella_gpu.h).  Same names, argument meaning and error behaviour as the
+// reference so that a maintainer (and the parity tests) can read one against the other:
+//
+//   count_kmers / KmerCounter::run      src/kmers/kmer_counting.rs:13-16, :41-123
+//   KmerFrequencyTable                  src/kmers/kmer_counting.rs:211-360
+//   ContigInformation, EmbedderEngine   src/embedding/embedder.rs:15-104
+//   KGraph / OutEdge                    annembed::fromhnsw::kgraph (third party; the subset the path uses)
+//   mutual_knn / intersect              src/graphs/nearest_neighbour_graph.rs:12-72
+//   RecoverEngine::build_mutual_kgraph  src/recover/recover_engine.rs:510-519 (k clamp)
+//
+// Errors: the reference returns anyhow::Result; here every failure throws rosella::Error (the C wrapper
+// in capi.cpp turns it into a status + message).  There is no CPU fallback: a Gpu is required.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <optional>
+#include <set>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/rosella_gpu.h"
+
+namespace rosella {
+
+struct Error : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+// one rg_handle = one GPU; not copyable, one caller thread at a time
+class Gpu {
+   public:
+    explicit Gpu(int device = 0);
+    ~Gpu();
+    Gpu(const Gpu &) = delete;
+    Gpu &operator=(const Gpu &) = delete;
+    rg_handle *raw() const { return h_; }
+    void check(int32_t rc, const char *what) const;
+
+   private:
+    rg_handle *h_ = nullptr;
+};
+
+// ------------------------------------------------------------------ FASTA/FASTQ (needletail::parse_fastx_file)
+struct FastxRecords {
+    std::vector<std::string> ids;      // header line without '>' / '@' (needletail SequenceRecord::id)
+    std::vector<uint8_t> seq;          // concatenated raw sequence bytes
+    std::vector<uint64_t> offsets;     // ids.size() + 1
+};
+FastxRecords parse_fastx_file(const std::string &path);   // plain or gzip; throws on malformed input
+
+// ------------------------------------------------------------------ KmerFrequencyTable (kmer_counting.rs:211-360)
+struct KmerFrequencyTable {
+    size_t kmer_size = 4;
+    size_t nrows = 0, ncols = 0;
+    std::vector<double> kmer_table;            // row-major nrows x ncols (ndarray standard layout)
+    std::vector<std::string> contig_names;
+    std::string table_path;
+
+    const double *row(size_t i) const { return kmer_table.data() + i * ncols; }
+    // :285-295 header-less CSV "name,v0,v1,..."; floats in shortest round-trip form (what csv + ryu write)
+    void write(const std::string &output_file);
+    // :298-333; apply_clr = the `no_flight` feature (:322-323)
+    static KmerFrequencyTable read(const std::string &input_file, bool apply_clr);
+    // :228-282; both return the names that were removed
+    std::set<std::string> filter_by_name(const std::set<std::string> &to_filter);
+    std::set<std::string> filter_by_index(const std::set<size_t> &indices_to_remove);
+    // :340-359  y = ln(x / mean(x)) per row
+    static void clr(std::vector<double> &table, size_t nrows, size_t ncols);
+};
+
+struct CountKmersArgs {          // the two clap arguments KmerCounter::new reads (:27-28)
+    std::string assembly;
+    std::string output_directory;
+};
+// count_kmers(m, n_contigs) (:13-16): reuses <out>/kmer_frequencies.tsv when present (:46-50), otherwise
+// reads the assembly, counts on the GPU, writes the table and reads it back (:117-120)
+KmerFrequencyTable count_kmers(Gpu &gpu, const CountKmersArgs &m, std::optional<size_t> n_contigs, bool no_flight);
+
+// ------------------------------------------------------------------ graph types (annembed KGraph subset)
+struct OutEdge {
+    size_t node;
+    double weight;
+};
+class KGraph {
+   public:
+    KGraph() = default;
+    KGraph(std::vector<std::vector<OutEdge>> neighbours, std::vector<size_t> data_ids, size_t max_nbng);
+    const std::vector<std::vector<OutEdge>> &get_neighbours() const { return neighbours_; }
+    size_t get_nb_nodes() const { return neighbours_.size(); }
+    size_t get_max_nbng() const { return max_nbng_; }
+    std::optional<size_t> get_data_id_from_idx(size_t idx) const;
+    std::optional<size_t> get_idx_from_dataid(size_t data_id) const;
+    std::vector<std::vector<OutEdge>> &neighbours_mut() { return neighbours_; }
+
+   private:
+    std::vector<std::vector<OutEdge>> neighbours_;
+    std::vector<size_t> data_ids_;      // IndexSet<DataId>: position = node index
+    size_t max_nbng_ = 0;
+};
+
+// embedder.rs:89-104 without the MinHash sketch
+struct ContigInformation {
+    const double *coverage;
+    size_t coverage_len;      // 2 x samples, interleaved mean,var
+    const double *tnf;
+    size_t tnf_len;
+};
+
+class EmbedderEngine {        // embedder.rs:15-87
+   public:
+    explicit EmbedderEngine(std::vector<std::vector<ContigInformation>> contig_information)
+        : contig_information(std::move(contig_information)) {}
+    // (kgraph, disconnected_nodes); max_layers / ef_construction / n_contigs are accepted and ignored (exact lists).
+    // As in the reference, the graph returned is the DEPTH kNN graph: intersect() and mutual_knn() are
+    // evaluated and their result dropped (nearest_neighbour_graph.rs:33,:70) unless apply_filters is set.
+    std::pair<KGraph, std::vector<size_t>> build_mutual_kgraph(Gpu &gpu, size_t keep_n_edges, size_t n_neighbours,
+                                                               size_t n_contigs, size_t max_layers,
+                                                               size_t ef_construction, bool apply_filters = false,
+                                                               uint32_t variant = RG_VARIANT_RUST) const;
+    std::vector<std::vector<ContigInformation>> contig_information;
+    // the TNF graph of the last build (the reference builds it as tnf_kgraph, :65)
+    mutable KGraph last_tnf_kgraph;
+};
+
+// nearest_neighbour_graph.rs:12-35 / :38-72.  apply = false reproduces the reference (result dropped).
+KGraph mutual_knn(Gpu &gpu, KGraph knn_graph, size_t keep_n_edges, bool apply = false);
+KGraph intersect(Gpu &gpu, KGraph base_knn_graph, const KGraph &intersecting_graph, size_t keep_n_edges, bool apply = false);
+
+// recover_engine.rs:513-517
+inline size_t clamp_n_neighbours(size_t n_included, size_t n_neighbours) {
+    return n_included < n_neighbours * 10 ? std::min(n_included / 2, n_neighbours) : n_neighbours;
+}
+
+std::string format_f64(double v);      // shortest round-trip text as Rust's csv/ryu writes it
+
+}  // namespace rosella
