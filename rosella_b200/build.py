@@ -17,6 +17,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall", "--
 EXTRA = {"knn_rescore.cu": ["-fmad=false"]}
 SOURCES = ["rg_api.cu", "knn_transform.cu", "knn_depth.cu", "knn_depth2.cu", "knn_tnf.cu", "knn_rescore.cu", "knn_search.cu",
            "tnf_count.cu", "tnf_api.cu", "graph_ops.cu", "tnf_host.cpp"]
+TOOLS = {"microbench.cu": "microbench", "microbench2.cu": "microbench2"}
 HEADERS = ["rg_internal.cuh", "pk.cuh", "tnf_tables.h", os.path.join("..", "..", "include", "rosella_gpu.h")]
 
 
@@ -65,6 +66,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if force or procs or _stale(LIB, objs):
         cmd = [nvcc, *_host_cxx(), *ARCH, "-shared", "-o", LIB, *objs, "-lpthread"]
         subprocess.check_call(cmd)
+    # stand-alone micro-benchmarks (bench.py's live FP32 peak; the issue-model probe)
+    for src, exe in TOOLS.items():
+        s, e = os.path.join(CSRC, src), os.path.join(OBJ, exe)
+        if force or _stale(e, [s]):
+            subprocess.check_call([nvcc, *_host_cxx(), *ARCH, "-O3", "-std=c++17", "-lineinfo", s, "-o", e])
     return LIB
 
 
