@@ -1,4 +1,5 @@
 // tnf_api.cu — C ABI of the TNF path (include/rosella_gpu.h, "TNF counting").
+#include <cstdlib>
 #include <vector>
 
 #include "rg_internal.cuh"
@@ -9,6 +10,17 @@ int32_t rg_tnf_launch_ascii(rg_handle *h);
 int32_t rg_tnf_launch_freq(rg_handle *h);
 uint32_t rg_tnf_chunk_words();
 uint32_t rg_tnf_chunk_bytes();
+// second generation (tnf_count2.cu): thread-private byte counters; the product path
+int32_t rg_tnf_launch_packed2(rg_handle *h);
+int32_t rg_tnf_launch_ascii2(rg_handle *h);
+uint32_t rg_tnf2_chunk_units();
+uint32_t rg_tnf2_seg_bytes();
+
+// RG_TNF_IMPL=1 selects the first-generation (shared-memory atomics) kernels for A/B measurements
+static bool use_v1() {
+    static const bool v1 = [] { const char *e = getenv("RG_TNF_IMPL"); return e && e[0] == '1'; }();
+    return v1;
+}
 
 static int32_t ensure_tables(rg_handle *h) {
     if (h->tnf_tables.p) return RG_OK;
@@ -20,11 +32,18 @@ static int32_t ensure_tables(rg_handle *h) {
     return RG_OK;
 }
 
-// exclusive scan of ceil(len/unit) over records -> device; lens given as an offsets array
-static int32_t upload_chunks(rg_handle *h, const uint64_t *offsets, uint64_t n, uint64_t unit) {
-    std::vector<uint64_t> start(n + 1);
+// exclusive scan of chunks per record -> device; lens given as an offsets array.  align = 0: a record of
+// len elements has ceil(len/unit) chunks; align > 0 (ASCII v2): the record owns the align-byte ALIGNED
+// segments it touches and a chunk holds `unit` of them.
+static int32_t upload_chunks(rg_handle *h, const uint64_t *offsets, uint64_t n, uint64_t unit, uint64_t align = 0) {
+    std::vector<uint64_t> start;
+    try { start.resize(n + 1); } catch (...) { return rg_fail(h, RG_ERR_OOM, "host allocation of %llu chunk offsets failed", (unsigned long long)(n + 1)); }
     start[0] = 0;
-    for (uint64_t r = 0; r < n; ++r) start[r + 1] = start[r] + (offsets[r + 1] - offsets[r] + unit - 1) / unit;
+    for (uint64_t r = 0; r < n; ++r) {
+        uint64_t len = offsets[r + 1] - offsets[r];
+        if (align && len) len = (offsets[r + 1] + align - 1) / align - offsets[r] / align;
+        start[r + 1] = start[r] + (len + unit - 1) / unit;
+    }
     h->tnf_chunks = start[n];
     RG_TRY(rg_reserve(h, h->chunk_start, (n + 1) * sizeof(uint64_t)));
     RG_CUDA(h, cudaMemcpyAsync(h->chunk_start.p, start.data(), (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
@@ -60,7 +79,7 @@ int32_t rg_tnf_load_packed(rg_handle *h, const uint64_t *codes, const uint32_t *
     RG_CUDA(h, cudaMemcpyAsync(h->valid.p, valid, words * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaMemcpyAsync(h->woff.p, word_offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
-    RG_TRY(upload_chunks(h, word_offsets, n, rg_tnf_chunk_words()));
+    RG_TRY(upload_chunks(h, word_offsets, n, use_v1() ? rg_tnf_chunk_words() : rg_tnf2_chunk_units()));
     h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.h2d_bytes += words * 12 + (n + 1) * 16;
     h->tnf_n = n; h->tnf_words = words; h->tnf_bytes = 0; h->tnf_mode = 1;
@@ -76,7 +95,7 @@ int32_t rg_tnf_load_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offs
         if (offsets[r + 1] < offsets[r]) return rg_fail(h, RG_ERR_INVALID, "rg_tnf_load_ascii: offsets must be non-decreasing");
     const uint64_t lo = n ? offsets[0] : 0, hi = n ? offsets[n] : 0;
     RG_TRY(ensure_tables(h));
-    RG_TRY(rg_reserve(h, h->ascii, hi));
+    RG_TRY(rg_reserve(h, h->ascii, (hi + 63) / 32 * 32));   // the v2 kernel reads whole aligned 32-byte segments
     RG_TRY(rg_reserve(h, h->aoff, (n + 1) * sizeof(uint64_t)));
     RG_TRY(reserve_outputs(h, n));
     RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
@@ -84,7 +103,8 @@ int32_t rg_tnf_load_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offs
         RG_CUDA(h, cudaMemcpyAsync((uint8_t *)h->ascii.p + lo, seq + lo, hi - lo, cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaMemcpyAsync(h->aoff.p, offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
-    RG_TRY(upload_chunks(h, offsets, n, rg_tnf_chunk_bytes()));
+    if (use_v1()) RG_TRY(upload_chunks(h, offsets, n, rg_tnf_chunk_bytes()));
+    else RG_TRY(upload_chunks(h, offsets, n, rg_tnf2_chunk_units(), rg_tnf2_seg_bytes()));
     h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.h2d_bytes += (hi - lo) + (n + 1) * 16;
     h->tnf_n = n; h->tnf_words = 0; h->tnf_bytes = hi - lo; h->tnf_mode = 2;
@@ -97,7 +117,8 @@ int32_t rg_tnf_count_resident(rg_handle *h) {
     RG_CUDA(h, cudaSetDevice(h->device));
     RG_CUDA(h, cudaMemsetAsync(h->counts.p, 0, h->tnf_n * RG_NBINS * sizeof(uint32_t), h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[6], h->stream));
-    RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed(h) : rg_tnf_launch_ascii(h));
+    if (use_v1()) RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed(h) : rg_tnf_launch_ascii(h));
+    else RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed2(h) : rg_tnf_launch_ascii2(h));
     RG_CUDA(h, cudaEventRecord(h->ev[7], h->stream));
     RG_TRY(rg_tnf_launch_freq(h));
     h->tm.tnf_count_ms = -1.0;   // resolved lazily by rg_get_timings

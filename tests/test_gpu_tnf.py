@@ -76,3 +76,29 @@ def test_large_properties(ctx):
     assert np.array_equal(c3, c) and np.array_equal(nk3, nk)
     want = oracle.tnf_count(seq, offs, fast=True)
     assert np.array_equal(c, want[0]) and np.array_equal(nk, want[1])
+
+
+def test_chunk_boundaries_and_many_short_records(ctx):
+    """Second-generation kernel (tnf_count2.cu): a chunk is 896 units of 32 bases (28 672 bases) per CTA step, a
+    thread's byte counters take at most 224 windows between flushes, and a CTA walks several records in a row."""
+    rng = np.random.default_rng(11)
+    alpha = np.frombuffer(b"ACGT", np.uint8)
+    recs = [bytes(alpha[rng.integers(0, 4, n)]) for n in (28671, 28672, 28673, 28675, 57344, 57347, 3 * 28672 + 5)]
+    recs += [b"T" * 28672 * 2, b"G" * 229, b"AC" * 14336 + b"N" + b"GT" * 7]       # saturating byte counters
+    recs += [bytes(alpha[rng.integers(0, 4, int(n))]) for n in rng.integers(0, 300, 3000)]   # record switches inside a CTA
+    long = alpha[rng.integers(0, 4, 400_000)].copy()
+    for p in rng.integers(0, 400_000 - 300, 40):
+        long[p:p + int(rng.integers(1, 200))] = ord("N")
+    long[rng.integers(0, 400_000, 4000)] |= 0x20                                      # lower case
+    recs.append(bytes(long))
+    offs = np.zeros(len(recs) + 1, np.uint64)
+    offs[1:] = np.cumsum([len(r) for r in recs])
+    seq = np.frombuffer(b"".join(recs), np.uint8)
+    _check(ctx, seq, offs)
+    # the same records behind an odd prefix: unaligned starts for the 32-byte segments of the ASCII kernel
+    for pad in (1, 17, 31):
+        seq2 = np.concatenate([np.full(pad, ord("A"), np.uint8), seq])
+        offs2 = offs + np.uint64(pad)
+        want = oracle.tnf_count(seq, offs, fast=True)
+        c, nk, _ = ctx.tnf_count_ascii(seq2, offs2)
+        assert np.array_equal(c, want[0]) and np.array_equal(nk, want[1])
