@@ -54,6 +54,9 @@ typedef enum {
 /* which kNN list */
 #define RG_GRAPH_TNF 0u        /* TNFDistance,   embedder.rs:41-48 (tnf_nn) */
 #define RG_GRAPH_DEPTH 1u      /* DepthDistance, embedder.rs:32-39 (depth_nn); MinHash factor = 1 */
+#define RG_GRAPH_TNF_EUCLID 2u /* Euclidean distance of the TNF rows as passed: flight's second TNF index,
+                                  flight/flight/rosella/embedding.py:163 (metrics.py:64-77); any variant;
+                                  a NaN distance (non-finite row) is reported as FLT_MAX */
 
 /* ------------------------------------------------------------------ lifecycle */
 int32_t rg_abi_version(void);

@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 NBINS = 136
 RUST, FLIGHT = 0, 1
-TNF, DEPTH = 0, 1
+TNF, DEPTH, TNF_EUCLID = 0, 1, 2
 
 
 def build(force: bool = False) -> str:

@@ -64,7 +64,8 @@ float orc_tnf_distance_f32(const double *x, const double *y, uint32_t d, int var
 float orc_depth_distance_f32(const double *a, const double *b, uint32_t s, int variant);
 
 /* Exhaustive exact top-k for query rows qrows[0..nq) (NULL = rows 0..nq) against all n rows.
- * which: 0 = TNF metric over tnf[n*d], 1 = depth metric over cov[n*2s].
+ * which: 0 = TNF metric over tnf[n*d], 1 = depth metric over cov[n*2s], 2 = Euclidean distance over
+ * tnf[n*d] (flight/flight/metrics.py:64-77, the index built at flight/flight/rosella/embedding.py:163).
  * Self excluded; ascending by (f32 distance, index); padding idx=UINT32_MAX, dist=+inf.
  * dist64 (optional) receives the untruncated f64 distances. */
 void orc_knn(const double *data, uint64_t n, uint32_t width, int which, int variant,

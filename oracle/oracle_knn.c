@@ -46,10 +46,15 @@ void orc_knn(const double *data, uint64_t n, uint32_t width, int which, int vari
                                                         : orc_kmer_correlation(qrow, rrow, width);
                     /* embedder.rs:122-125 (same guards as orc_tnf_distance_f32) */
                     d = isnan(d64) ? (variant == ORC_VARIANT_RUST ? 0.0f : 2.0f) : (float)d64;
-                } else {
+                } else if (which == 1) {
                     d64 = orc_metabat(qrow, rrow, width / 2, variant);
                     /* embedder.rs:165-170, MinHash factor 1.0 */
                     d = isnan(d64) ? 1.0f : (float)d64;
+                } else {
+                    /* flight's second TNF index, rosella/embedding.py:163 (metrics.tnf_euclidean);
+                     * a NaN distance (non-finite row) is defined as the largest finite f32 */
+                    d64 = orc_tnf_euclidean(qrow, rrow, width);
+                    d = isnan(d64) ? 3.402823466e+38f : (float)d64;
                 }
                 if (cnt == k && !cand_less(d, (uint32_t)j, best[k - 1].d, best[k - 1].i)) continue;
                 uint32_t p = cnt < k ? cnt : k - 1;

@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librosella_gpu.so")
 NBINS = 136
 VARIANT_RUST, VARIANT_FLIGHT = 0, 1
-GRAPH_TNF, GRAPH_DEPTH = 0, 1
+GRAPH_TNF, GRAPH_DEPTH, GRAPH_TNF_EUCLID = 0, 1, 2
 
 # every symbol include/rosella_gpu.h declares (tests check the .so exports exactly these)
 SYMBOLS = [

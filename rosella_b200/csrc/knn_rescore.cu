@@ -55,6 +55,13 @@ __device__ double rho_flight_f64(const double *__restrict__ x, const double *__r
     return 2.0 - rho;
 }
 
+// flight/flight/metrics.py:64-77 (tnf_euclidean)
+__device__ double tnf_euclidean_f64(const double *__restrict__ x, const double *__restrict__ y, uint32_t d) {
+    double r = 0.0;
+    for (uint32_t j = 0; j < d; ++j) r += (x[j] - y[j]) * (x[j] - y[j]);
+    return sqrt(r);
+}
+
 // statrs Normal::cdf (call sites coverage_calculator.rs:647,:650)
 __device__ __forceinline__ double cdf_statrs(double mean, double sd, double x) {
     return 0.5 * erfc((mean - x) / (sd * 1.4142135623730951));
@@ -131,7 +138,10 @@ rescore_kernel(const double *__restrict__ data, uint32_t n, uint32_t width, cons
         if (j < n) {
             const double *rrow = data + (uint64_t)j * width;
             double v;
-            if (WHICH == RG_GRAPH_TNF) {
+            if (WHICH == RG_GRAPH_TNF_EUCLID) {
+                v = tnf_euclidean_f64(qrow, rrow, width);
+                df = isnan(v) ? 3.402823466e+38f : (float)v;
+            } else if (WHICH == RG_GRAPH_TNF) {
                 v = VARIANT == RG_VARIANT_FLIGHT ? rho_flight_f64(qrow, rrow, width) : kmer_correlation_f64(qrow, rrow, width);
                 // embedder.rs:122-125; FLIGHT: NaN is defined as the metric's maximum
                 df = isnan(v) ? (VARIANT == RG_VARIANT_RUST ? 0.0f : 2.0f) : (float)v;
@@ -183,7 +193,7 @@ int32_t launch_rescore(rg_handle *h, const double *data, uint32_t width, uint32_
 }  // namespace
 
 int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
-int32_t rg_launch_tnf_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
+int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 
 // K' = candidates kept by the FP32 select phase: k plus a margin that absorbs FP32 reordering
 static uint32_t pick_kprime(uint32_t k) {
@@ -197,8 +207,8 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
                                      uint32_t *idx_dev, float *dist_dev, uint32_t *n_valid_dev) {
     if (!h) return RG_ERR_INVALID;
     if (h->n == 0) return rg_fail(h, RG_ERR_STATE, "rg_knn_search: no tables loaded (call rg_knn_load first)");
-    if (which > RG_GRAPH_DEPTH) return rg_fail(h, RG_ERR_INVALID, "rg_knn_search: unknown graph %u", which);
-    if (which == RG_GRAPH_TNF && !h->has_tnf) return rg_fail(h, RG_ERR_STATE, "rg_knn_search: no TNF table loaded");
+    if (which > RG_GRAPH_TNF_EUCLID) return rg_fail(h, RG_ERR_INVALID, "rg_knn_search: unknown graph %u", which);
+    if (which != RG_GRAPH_DEPTH && !h->has_tnf) return rg_fail(h, RG_ERR_STATE, "rg_knn_search: no TNF table loaded");
     if (which == RG_GRAPH_DEPTH && !h->has_cov) return rg_fail(h, RG_ERR_STATE, "rg_knn_search: no coverage table loaded");
     if (!idx_dev || !dist_dev) return rg_fail(h, RG_ERR_INVALID, "rg_knn_search: output pointer is NULL");
     if (q_begin > q_end || q_end > h->n)
@@ -213,13 +223,15 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
     RG_TRY(rg_reserve(h, h->cand_i, q_count * kprime * sizeof(uint32_t)));
     RG_CUDA(h, cudaEventRecord(h->ev[3], h->stream));
     if (which == RG_GRAPH_DEPTH) RG_TRY(rg_launch_depth_select(h, kprime, q_begin, q_count));
-    else RG_TRY(rg_launch_tnf_select(h, kprime, q_begin, q_count));
+    else RG_TRY(rg_launch_tnf_select(h, which, kprime, q_begin, q_count));
     RG_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
     const bool fl = h->variant == RG_VARIANT_FLIGHT;
     if (which == RG_GRAPH_DEPTH) {
         const double *data = (const double *)h->cov64.p;
         RG_TRY(fl ? (launch_rescore<RG_VARIANT_FLIGHT, RG_GRAPH_DEPTH>(h, data, 2 * h->s, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev))
                   : (launch_rescore<RG_VARIANT_RUST, RG_GRAPH_DEPTH>(h, data, 2 * h->s, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev)));
+    } else if (which == RG_GRAPH_TNF_EUCLID) {
+        RG_TRY((launch_rescore<RG_VARIANT_FLIGHT, RG_GRAPH_TNF_EUCLID>(h, (const double *)h->tnf64.p, h->d, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev)));
     } else {
         const double *data = (const double *)h->tnf64.p;
         RG_TRY(fl ? (launch_rescore<RG_VARIANT_FLIGHT, RG_GRAPH_TNF>(h, data, h->d, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev))

@@ -16,11 +16,19 @@ constexpr int QPW = 8;
 constexpr int WARPS = 8;
 constexpr int QB = QPW * WARPS;   // 64 query rows per CTA
 
+// VARIANT 2 = squared Euclidean distance of the rows as passed (RG_GRAPH_TNF_EUCLID; flight/flight/metrics.py:64-77):
+// |x - y|^2 = |x~|^2 + |y~|^2 - 2 x~.y~ + d (mean_x - mean_y)^2 on the centred rows; selection only needs the order,
+// so the square root is left to the f64 re-evaluation.
+constexpr int METRIC_EUCLID = 2;
+
 template <int VARIANT>
-__device__ __forceinline__ float tnf_finish(float dot, float nq, float nr) {
+__device__ __forceinline__ float tnf_finish(float dot, float nq, float nr, float dmu2) {
     const float den = nq + nr;                      // NaN when either row is flagged non-finite
     float d;
-    if (VARIANT == RG_VARIANT_RUST) {
+    if (VARIANT == METRIC_EUCLID) {
+        d = fmaxf(fmaf(-2.0f, dot, den) + dmu2, 0.f);
+        if (den != den) d = 3.402823466e+38f;       // non-finite row: the defined maximum (include/rosella_gpu.h)
+    } else if (VARIANT == RG_VARIANT_RUST) {
         d = 0.5f - __fdividef(dot, den);
         if (dot == 0.f) d = 1.0f;                   // :385
         if (nq == 0.f && nr == 0.f) d = 0.f;        // :383
@@ -34,7 +42,8 @@ __device__ __forceinline__ float tnf_finish(float dot, float nq, float nr) {
 
 template <int VARIANT, int K, int RR>
 __global__ void __launch_bounds__(WARPS * 32, 1)
-tnf_select_kernel(const float4 *__restrict__ tnf_t, const float *__restrict__ norm, uint32_t n, uint32_t D4,
+tnf_select_kernel(const float4 *__restrict__ tnf_t, const float *__restrict__ norm, const float *__restrict__ mean,
+                  uint32_t n, uint32_t D4,
                   uint32_t n_tiles, uint32_t q_begin, uint32_t q_count, float *__restrict__ cand_d,
                   uint32_t *__restrict__ cand_i) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -79,12 +88,14 @@ tnf_select_kernel(const float4 *__restrict__ tnf_t, const float *__restrict__ no
     };
     if (tid == 0) issue(0);
 
-    float thr[QPW], nq[QPW];
+    float thr[QPW], nq[QPW], mq[QPW];
 #pragma unroll
     for (int u = 0; u < QPW; ++u) {
         thr[u] = INFINITY;
         nq[u] = qn[warp * QPW + u];
+        mq[u] = VARIANT == METRIC_EUCLID ? mean[min(q0 + warp * QPW + u, n - 1)] : 0.f;
     }
+    const float dim = (float)(D4 * 4);
 
     for (uint32_t st = 0; st < n_stages; ++st) {
         __syncthreads();
@@ -118,10 +129,12 @@ tnf_select_kernel(const float4 *__restrict__ tnf_t, const float *__restrict__ no
         for (int g = 0; g < RR; ++g) {
             const uint32_t ridx = (st * RR + g) * RG_TILE + lane;
             const float nr = ridx < n ? norm[ridx] : 0.f;
+            const float mr = (VARIANT == METRIC_EUCLID && ridx < n) ? mean[ridx] : 0.f;
 #pragma unroll
             for (int u = 0; u < QPW; ++u) {
                 const uint32_t qrow = q0 + warp * QPW + u;
-                float d = tnf_finish<VARIANT>(acc[u][g], nq[u], nr);
+                const float dm = mq[u] - mr;
+                float d = tnf_finish<VARIANT>(acc[u][g], nq[u], nr, dim * dm * dm);
                 if (ridx >= n || ridx == qrow || qrow >= q_end) d = INFINITY;
                 topk_offer<K>(list_d + (warp * QPW + u) * K, list_i + (warp * QPW + u) * K, d, ridx, thr[u], lane);
             }
@@ -151,7 +164,7 @@ int32_t launch(rg_handle *h, uint64_t q_begin, uint64_t q_count) {
     RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = (unsigned)((q_count + QB - 1) / QB);
     kern<<<grid, WARPS * 32, smem, h->stream>>>((const float4 *)h->tnf_t.p, (const float *)h->tnf_norm.p,
-                                                (uint32_t)h->n, D4, (uint32_t)h->n_tiles, (uint32_t)q_begin,
+                                                (const float *)h->tnf_mean.p, (uint32_t)h->n, D4, (uint32_t)h->n_tiles, (uint32_t)q_begin,
                                                 (uint32_t)q_count, (float *)h->cand_d.p, (uint32_t *)h->cand_i.p);
     RG_CUDA(h, cudaGetLastError());
     h->tm.kernel_launches += 1;
@@ -170,7 +183,8 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 
 }  // namespace
 
-int32_t rg_launch_tnf_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    if (which == RG_GRAPH_TNF_EUCLID) return launch_k<METRIC_EUCLID>(h, kprime, q_begin, q_count);
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);
 }

@@ -10,7 +10,7 @@
 #include "rg_internal.cuh"
 
 __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n, uint32_t d,
-                                     float *__restrict__ out, float *__restrict__ norm) {
+                                     float *__restrict__ out, float *__restrict__ norm, float *__restrict__ mean) {
     const int lane = threadIdx.x & 31;
     const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const uint64_t rows_padded = (n + RG_TILE - 1) / RG_TILE * RG_TILE;
@@ -46,7 +46,10 @@ __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n,
     bad = __any_sync(0xffffffffu, bad);
     // a row with a non-finite centred value (ln 0 in the CLR, kmer_counting.rs:351) is stored as zeros
     // with a NaN norm: every distance to it becomes NaN -> 1.0 exactly as :410 does in f64
-    if (lane == 0) norm[row] = bad ? __int_as_float(0x7fc00000) : (float)nn;
+    if (lane == 0) {
+        norm[row] = bad ? __int_as_float(0x7fc00000) : (float)nn;
+        mean[row] = row < n && isfinite(mu) ? (float)mu : 0.f;
+    }
 }
 
 __global__ void cov_transform_kernel(const double *__restrict__ cov, uint64_t n, uint32_t s, uint32_t variant,
@@ -99,6 +102,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
         RG_TRY(rg_reserve(h, h->tnf64, n * d * sizeof(double)));
         RG_TRY(rg_reserve(h, h->tnf_t, rows_padded * d * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_norm, rows_padded * sizeof(float)));
+        RG_TRY(rg_reserve(h, h->tnf_mean, rows_padded * sizeof(float)));
         RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         h->tm.h2d_bytes += n * d * sizeof(double);
     }
@@ -112,7 +116,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     if (tnf) {
         const int wpb = 8;
         tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
-            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p);
+            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p);
         RG_CUDA(h, cudaGetLastError());
         h->tm.kernel_launches += 1;
     }

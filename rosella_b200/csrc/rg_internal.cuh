@@ -33,6 +33,7 @@ struct rg_handle {
     DevBuf tnf64, cov64;      // the caller's f64 tables, kept for the f64 re-evaluation
     DevBuf tnf_t;             // f32 centred rows, tile-major [tile][d/4][32] float4
     DevBuf tnf_norm;          // f32 [n_tiles*32] sum of squares of the centred row (NaN = non-finite row)
+    DevBuf tnf_mean;          // f32 [n_tiles*32] mean of the row as passed (Euclidean graph)
     DevBuf cov_t;             // float4 (mean, var, ln var, +-1/(sd*sqrt2)) tile-major [tile][s][32]
     DevBuf err_flag;          // u32 device error word (non-finite coverage, ...)
     DevBuf cand_d, cand_i;    // select-phase candidates [rows][kprime]

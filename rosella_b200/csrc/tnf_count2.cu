@@ -134,16 +134,27 @@ tnf_count_packed2_kernel(const uint64_t *__restrict__ codes, const uint32_t *__r
         }
         const uint64_t rec_w0 = woff[cur.rec], rec_w1 = woff[cur.rec + 1];
         const uint64_t w0 = rec_w0 + (chunk - chunk_start[cur.rec]) * UNIT_PER_CHUNK + tid;
+        // software pipeline of depth 1: the loads of word i+1 are in flight while word i is counted (a word is
+        // ~32 dependent shared-memory updates, far longer than a DRAM round trip)
+        uint64_t c = 0, cp = 0;
+        uint32_t v = 0, vp = 0;
+        auto fetch = [&](uint64_t w) {
+            if (w < rec_w1) {
+                c = codes[w];
+                v = valid[w];
+                if (w > rec_w0) { cp = codes[w - 1]; vp = valid[w - 1]; }   // last 3 bases of the previous word of this record
+                else { cp = 0; vp = 0; }
+            }
+        };
+        fetch(w0);
 #pragma unroll 1
         for (int i = 0; i < WPT; ++i) {
             const uint64_t w = w0 + (uint64_t)i * T2;
-            if (w < rec_w1) {
-                const uint64_t c = codes[w];
-                const uint32_t v = valid[w];
-                uint32_t pc = 0, pv = 0;                            // last 3 bases of the previous word of this record
-                if (w > rec_w0) { pc = (uint32_t)(codes[w - 1] >> 58); pv = valid[w - 1] >> 29; }
-                count_word(cb, tb, c, v, pc, pv);
-            }
+            if (w >= rec_w1) break;
+            const uint64_t c_now = c;
+            const uint32_t v_now = v, pc = (uint32_t)(cp >> 58), pv = vp >> 29;
+            if (i + 1 < WPT) fetch(w + T2);
+            count_word(cb, tb, c_now, v_now, pc, pv);
         }
         fold_counters(sm, tid);
     }

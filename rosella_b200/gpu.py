@@ -7,9 +7,9 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import GRAPH_DEPTH, GRAPH_TNF, NBINS, VARIANT_FLIGHT, VARIANT_RUST, RosellaGpuError, Timings
+from ._lib import GRAPH_DEPTH, GRAPH_TNF, GRAPH_TNF_EUCLID, NBINS, VARIANT_FLIGHT, VARIANT_RUST, RosellaGpuError, Timings
 
-__all__ = ["Context", "canonical_kmers", "pack_host", "GRAPH_TNF", "GRAPH_DEPTH", "VARIANT_RUST", "VARIANT_FLIGHT"]
+__all__ = ["Context", "canonical_kmers", "pack_host", "GRAPH_TNF", "GRAPH_DEPTH", "GRAPH_TNF_EUCLID", "VARIANT_RUST", "VARIANT_FLIGHT"]
 
 
 def canonical_kmers() -> list[str]:

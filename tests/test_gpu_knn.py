@@ -25,6 +25,9 @@ PAD = 0xFFFFFFFF
 
 
 def _pair_dist(data, which, variant, i, j):
+    if which == oracle.TNF_EUCLID:
+        v = oracle.tnf_euclidean(data[i], data[j])
+        return np.float32(3.402823466e+38) if np.isnan(v) else np.float32(v)
     if which == oracle.TNF:
         v = oracle.rho_flight(data[i], data[j]) if variant == oracle.FLIGHT else oracle.kmer_correlation(data[i], data[j])
         if np.isnan(v):
@@ -93,6 +96,31 @@ def test_knn_sharded_query_ranges(ctx):
     check_against_oracle(tnf, oracle.TNF, oracle.RUST, 10, ti, td, q_begin=777)
     e_i, e_d, _ = ctx.knn_search(gpu.GRAPH_TNF, 10, 5, 5)
     assert e_i.shape == (0, 10)
+
+
+def test_knn_tnf_euclidean(ctx, golden_dir):
+    """flight's second TNF index (rosella/embedding.py:163, metrics.tnf_euclidean): Euclidean distance of the rows as
+    passed, for both TNF flavours (CLR rows have mean 0; raw frequency rows do not), and the reference's own
+    numba outputs for all pairs."""
+    for flight in (False, True):
+        tnf, _, _ = synth.knn_tables(2500, 2, seed=21, flight=flight)
+        ctx.knn_load(tnf, None, gpu.VARIANT_FLIGHT if flight else gpu.VARIANT_RUST)
+        idx, dist, nv = ctx.knn_search(gpu.GRAPH_TNF_EUCLID, 30)
+        assert (nv == 30).all()
+        r, e = check_against_oracle(tnf, oracle.TNF_EUCLID, oracle.FLIGHT, 30, idx, dist)
+        assert e > 0.99
+    freq = np.exp(tnf[:800]); freq /= freq.sum(axis=1, keepdims=True)      # uncentred rows: the mean term matters
+    freq[:, 0] += np.linspace(0.0, 0.05, 800)
+    ctx.knn_load(freq, None, gpu.VARIANT_FLIGHT)
+    idx, dist, _ = ctx.knn_search(gpu.GRAPH_TNF_EUCLID, 15, 100, 500)
+    check_against_oracle(freq, oracle.TNF_EUCLID, oracle.FLIGHT, 15, idx, dist, q_begin=100)
+    g = np.load(os.path.join(golden_dir, "flight_metrics.npz"))
+    x, ref = g["tnf_clr"], g["tnf_euclidean"]
+    ctx.knn_load(x, None, gpu.VARIANT_FLIGHT)
+    idx, dist, _ = ctx.knn_search(gpu.GRAPH_TNF_EUCLID, len(x) - 1)
+    for i in range(len(x)):
+        want = ref[i][idx[i]].astype(np.float32)
+        assert np.all(np.abs(dist[i] - want) <= TAU_REL * np.abs(want) + 1e-12)
 
 
 @pytest.mark.parametrize("k,n", [(1, 300), (48, 400), (100, 700), (200, 600)])
