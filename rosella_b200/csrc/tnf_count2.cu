@@ -210,10 +210,21 @@ tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restr
         const uint64_t rb = offsets[cur.rec], re = offsets[cur.rec + 1];
         const uint64_t u_end = (re + SEG_BYTES - 1) / SEG_BYTES;
         const uint64_t u0 = rb / SEG_BYTES + (chunk - chunk_start[cur.rec]) * UNIT_PER_CHUNK + tid;
+        // depth-1 software pipeline of the two 16-byte loads of a unit
+        uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+        if (u0 < u_end) {
+            n0 = *reinterpret_cast<const uint4 *>(seq + u0 * SEG_BYTES);
+            n1 = *reinterpret_cast<const uint4 *>(seq + u0 * SEG_BYTES + 16);
+        }
 #pragma unroll 1
         for (int i = 0; i < WPT; ++i) {
             const uint64_t u = u0 + (uint64_t)i * T2;
             if (u >= u_end) break;
+            const uint4 q0 = n0, q1 = n1;
+            if (i + 1 < WPT && u + T2 < u_end) {
+                n0 = *reinterpret_cast<const uint4 *>(seq + (u + T2) * SEG_BYTES);
+                n1 = *reinterpret_cast<const uint4 *>(seq + (u + T2) * SEG_BYTES + 16);
+            }
             const uint64_t base = u * SEG_BYTES;
             const uint64_t p0 = max(base, rb), p1 = min(base + SEG_BYTES, re);
             // rebuild the rolling state from the (up to) 3 kept bytes before p0
@@ -229,8 +240,6 @@ tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restr
                 if (back[k] < 4) { st.code7 = (st.code7 >> 2) | ((uint32_t)back[k] << 13); st.run += 1; }
                 else st.run = 0;
             }
-            const uint4 q0 = *reinterpret_cast<const uint4 *>(seq + base);
-            const uint4 q1 = *reinterpret_cast<const uint4 *>(seq + base + 16);
             const uint32_t wd[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
             if (p0 == base && p1 == base + SEG_BYTES) {
 #pragma unroll
