@@ -182,7 +182,7 @@ def main_ours(args):
                 "d2h_bytes_per_step": r["d2h_per_step"],
                 "note": "every step re-loads both f64 tables from pinned host memory (rg_knn_load) and returns host lists"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
-        "roofline": {"kernel": "depth_select_kernel", "bound": "fp32", "achieved": ach, "peak": fp32,
+        "roofline": {"kernel": "depth_select2_kernel", "bound": "fp32", "achieved": ach, "peak": fp32,
                      "unit": "TFLOP/s", "frac": (ach / fp32) if fp32 else None, "traffic": None,
                      "peak_source": "live FFMA micro-benchmark (rosella_b200/csrc/microbench.cu); MEASURED_PEAKS.json has no FP32 CUDA-core entry",
                      "algorithmic_flops_per_launch": r["flops_depth"], "launch_ms": r["depth_sel_ms"]},
