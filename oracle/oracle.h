@@ -45,6 +45,7 @@ void orc_tnf_count_fast(const uint8_t *seq, const uint64_t *offsets, uint64_t n,
                         uint32_t *counts, uint64_t *n_kmers, double *freqs, int threads);
 
 /* kmer_counting.rs:340-359 — CLR in place semantics: y_j = ln(x_j / mean(x)). */
+double orc_ndarray_sum(const double *xs, uint32_t len);
 void orc_clr(const double *in, double *out, uint64_t n, uint32_t d);
 /* flight binning.py:192 — clr(x + 1) (skbio clr: ln x - mean(ln x)). */
 void orc_clr_flight(const double *in, double *out, uint64_t n, uint32_t d);

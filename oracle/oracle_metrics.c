@@ -22,12 +22,28 @@ int orc_max_threads(void) {
 #endif
 }
 
+/* ndarray ^0.15 ArrayBase::sum on a contiguous row = numeric_util::unrolled_fold: eight partial sums over
+ * strides of 8, combined as acc += (p0+p4); acc += (p1+p5); acc += (p2+p6); acc += (p3+p7); then the (< 8)
+ * remaining elements in order.  The crate is not under /root/reference: restated from the
+ * published source; the call site is kmer_counting.rs:345 (row.sum()). */
+double orc_ndarray_sum(const double *xs, uint32_t len) {
+    double p[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc = 0.0;
+    uint32_t i = 0;
+    for (; i + 8 <= len; i += 8)
+        for (int l = 0; l < 8; ++l) p[l] = p[l] + xs[i + l];
+    acc = acc + (p[0] + p[4]);
+    acc = acc + (p[1] + p[5]);
+    acc = acc + (p[2] + p[6]);
+    acc = acc + (p[3] + p[7]);
+    for (; i < len; ++i) acc = acc + xs[i];
+    return acc;
+}
+
 /* kmer_counting.rs:340-359 */
 void orc_clr(const double *in, double *out, uint64_t n, uint32_t d) {
     for (uint64_t r = 0; r < n; ++r) {
         const double *row = in + r * d;
-        double sum = 0.0;
-        for (uint32_t j = 0; j < d; ++j) sum += row[j];
+        double sum = orc_ndarray_sum(row, d);
         double mean = sum / (double)d;
         for (uint32_t j = 0; j < d; ++j) out[r * d + j] = log(row[j] / mean);
     }

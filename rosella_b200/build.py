@@ -10,6 +10,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "librosella_gpu.so")
+HOST_DIR = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(HERE, "librosella_host.so")
+HOST_SOURCES = ["kmer_table.cpp", "fastx.cpp", "embedder.cpp", "capi.cpp"]
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall", "--expt-relaxed-constexpr"]
@@ -66,6 +69,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if force or procs or _stale(LIB, objs):
         cmd = [nvcc, *_host_cxx(), *ARCH, "-shared", "-o", LIB, *objs, "-lpthread"]
         subprocess.check_call(cmd)
+    # C++ host mirror of the reference interface (host/rosella_host.hpp), on top of the C ABI
+    hsrc = [os.path.join(HOST_DIR, f) for f in HOST_SOURCES]
+    hdeps = hsrc + [os.path.join(HOST_DIR, "rosella_host.hpp"), os.path.join(HERE, "..", "include", "rosella_gpu.h"), LIB]
+    if force or _stale(HOST_LIB, hdeps):
+        subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-std=c++17", "-fPIC",
+                               "-Wall", "-shared", "-o", HOST_LIB, *hsrc, "-L" + HERE, "-lrosella_gpu", "-lz",
+                               "-Wl,-rpath,$ORIGIN"])
     # stand-alone micro-benchmarks (bench.py's live FP32 peak; the issue-model probe)
     for src, exe in TOOLS.items():
         s, e = os.path.join(CSRC, src), os.path.join(OBJ, exe)

@@ -1,0 +1,216 @@
+"""ctypes view of librosella_host.so — the C++ mirror of the reference's Rust interface for the hot path
+(rosella_b200/host/rosella_host.hpp: KmerFrequencyTable, count_kmers, EmbedderEngine::build_mutual_kgraph,
+mutual_knn / intersect, KGraph).  Used by the tests so that they read like tests of the reference's own API;
+C++ callers include rosella_host.hpp, the Rust shim binds include/rosella_gpu.h directly."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librosella_host.so")
+_lib = None
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -m rosella_b200.build`")
+    C.CDLL(os.path.join(_HERE, "librosella_gpu.so"), mode=C.RTLD_GLOBAL)
+    lib = C.CDLL(LIB_PATH)
+    vp, sz, dp = C.c_void_p, C.c_size_t, C.POINTER(C.c_double)
+    sig = {
+        "rh_last_error": (C.c_char_p, []),
+        "rh_format_f64": (C.c_int, [C.c_double, C.c_char_p, sz]),
+        "rh_clamp_n_neighbours": (sz, [sz, sz]),
+        "rh_table_new": (vp, [dp, sz, sz, C.POINTER(C.c_char_p)]),
+        "rh_table_free": (None, [vp]),
+        "rh_table_write": (C.c_int, [vp, C.c_char_p]),
+        "rh_table_read": (vp, [C.c_char_p, C.c_int]),
+        "rh_table_nrows": (sz, [vp]), "rh_table_ncols": (sz, [vp]), "rh_table_kmer_size": (sz, [vp]),
+        "rh_table_data": (dp, [vp]), "rh_table_name": (C.c_char_p, [vp, sz]), "rh_table_path": (C.c_char_p, [vp]),
+        "rh_table_filter_by_index": (C.c_long, [vp, C.POINTER(sz), sz]),
+        "rh_table_filter_by_name": (C.c_long, [vp, C.POINTER(C.c_char_p), sz]),
+        "rh_clr": (C.c_int, [dp, sz, sz]),
+        "rh_fastx_parse": (vp, [C.c_char_p]), "rh_fastx_free": (None, [vp]), "rh_fastx_n": (sz, [vp]),
+        "rh_fastx_id": (C.c_char_p, [vp, sz]), "rh_fastx_seq": (C.POINTER(C.c_uint8), [vp]),
+        "rh_fastx_offsets": (C.POINTER(C.c_uint64), [vp]),
+        "rh_count_kmers": (vp, [C.c_int, C.c_char_p, C.c_char_p, C.c_int]),
+        "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32]),
+        "rh_graph_free": (None, [vp]), "rh_graph_nb_nodes": (sz, [vp]), "rh_graph_max_nbng": (sz, [vp]),
+        "rh_graph_n_disconnected": (sz, [vp]), "rh_graph_disconnected": (C.POINTER(sz), [vp]),
+        "rh_graph_degree": (sz, [vp, C.c_int, sz]),
+        "rh_graph_neighbours": (C.c_int, [vp, C.c_int, sz, C.POINTER(sz), dp]),
+        "rh_graph_data_id_from_idx": (C.c_long, [vp, sz]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(lib, name)
+        f.restype, f.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def _err() -> HostError:
+    return HostError(load().rh_last_error().decode())
+
+
+def format_f64(v: float) -> str:
+    buf = C.create_string_buffer(64)
+    if load().rh_format_f64(v, buf, 64):
+        raise _err()
+    return buf.value.decode()
+
+
+def clamp_n_neighbours(n_included: int, n_neighbours: int) -> int:
+    return load().rh_clamp_n_neighbours(n_included, n_neighbours)
+
+
+def clr(table: np.ndarray) -> np.ndarray:
+    t = np.ascontiguousarray(table, np.float64).copy()
+    if load().rh_clr(t.ctypes.data_as(C.POINTER(C.c_double)), t.shape[0], t.shape[1]):
+        raise _err()
+    return t
+
+
+class KmerFrequencyTable:
+    """kmer_counting.rs:211-360"""
+
+    def __init__(self, handle):
+        if not handle:
+            raise _err()
+        self._h = handle
+
+    @classmethod
+    def new(cls, table: np.ndarray, names: list[str]):
+        t = np.ascontiguousarray(table, np.float64)
+        arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+        return cls(load().rh_table_new(t.ctypes.data_as(C.POINTER(C.c_double)), t.shape[0], t.shape[1], arr))
+
+    @classmethod
+    def read(cls, path: str, apply_clr: bool = False):
+        return cls(load().rh_table_read(path.encode(), int(apply_clr)))
+
+    def write(self, path: str):
+        if load().rh_table_write(self._h, path.encode()):
+            raise _err()
+
+    @property
+    def kmer_table(self) -> np.ndarray:
+        lib = load()
+        n, m = lib.rh_table_nrows(self._h), lib.rh_table_ncols(self._h)
+        if n * m == 0:
+            return np.zeros((n, m))
+        return np.ctypeslib.as_array(lib.rh_table_data(self._h), shape=(n, m)).copy()
+
+    @property
+    def contig_names(self) -> list[str]:
+        lib = load()
+        return [lib.rh_table_name(self._h, i).decode() for i in range(lib.rh_table_nrows(self._h))]
+
+    @property
+    def kmer_size(self) -> int:
+        return load().rh_table_kmer_size(self._h)
+
+    @property
+    def table_path(self) -> str:
+        return load().rh_table_path(self._h).decode()
+
+    def filter_by_index(self, indices) -> int:
+        idx = (C.c_size_t * len(indices))(*sorted(indices))
+        r = load().rh_table_filter_by_index(self._h, idx, len(indices))
+        if r < 0:
+            raise _err()
+        return r
+
+    def filter_by_name(self, names) -> int:
+        arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+        r = load().rh_table_filter_by_name(self._h, arr, len(names))
+        if r < 0:
+            raise _err()
+        return r
+
+    def __del__(self):
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.rh_table_free(self._h)
+            self._h = None
+
+
+def parse_fastx_file(path: str):
+    """-> (ids, seq u8, offsets u64) as needletail::parse_fastx_file yields the records"""
+    lib = load()
+    h = lib.rh_fastx_parse(path.encode())
+    if not h:
+        raise _err()
+    try:
+        n = lib.rh_fastx_n(h)
+        ids = [lib.rh_fastx_id(h, i).decode() for i in range(n)]
+        offs = np.ctypeslib.as_array(lib.rh_fastx_offsets(h), shape=(n + 1,)).copy()
+        seq = np.ctypeslib.as_array(lib.rh_fastx_seq(h), shape=(int(offs[-1]),)).copy() if offs[-1] else np.zeros(0, np.uint8)
+        return ids, seq, offs
+    finally:
+        lib.rh_fastx_free(h)
+
+
+def count_kmers(assembly: str, output_directory: str, no_flight: bool = False, device: int = 0) -> KmerFrequencyTable:
+    """count_kmers(m, n_contigs) (kmer_counting.rs:13-16) on the GPU"""
+    return KmerFrequencyTable(load().rh_count_kmers(device, assembly.encode(), output_directory.encode(), int(no_flight)))
+
+
+class KGraphResult:
+    """(KGraph<f64>, disconnected_nodes) of EmbedderEngine::build_mutual_kgraph plus the TNF kgraph of the build"""
+
+    def __init__(self, handle):
+        if not handle:
+            raise _err()
+        self._h = handle
+
+    @property
+    def nb_nodes(self) -> int:
+        return load().rh_graph_nb_nodes(self._h)
+
+    @property
+    def max_nbng(self) -> int:
+        return load().rh_graph_max_nbng(self._h)
+
+    @property
+    def disconnected_nodes(self) -> list[int]:
+        lib = load()
+        n = lib.rh_graph_n_disconnected(self._h)
+        p = lib.rh_graph_disconnected(self._h)
+        return [int(p[i]) for i in range(n)]
+
+    def neighbours(self, node: int, tnf: bool = False):
+        lib = load()
+        deg = lib.rh_graph_degree(self._h, int(tnf), node)
+        nodes = (C.c_size_t * max(deg, 1))()
+        w = (C.c_double * max(deg, 1))()
+        if lib.rh_graph_neighbours(self._h, int(tnf), node, nodes, w):
+            raise _err()
+        return np.array(nodes[:deg], np.int64), np.array(w[:deg], np.float64)
+
+    def data_id_from_idx(self, idx: int) -> int:
+        return load().rh_graph_data_id_from_idx(self._h, idx)
+
+    def __del__(self):
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.rh_graph_free(self._h)
+            self._h = None
+
+
+def build_mutual_kgraph(tnf: np.ndarray, cov: np.ndarray, keep_n_edges: int, n_neighbours: int, max_layers: int = 16,
+                        ef_construction: int = 200, apply_filters: bool = False, variant: int = 0, device: int = 0):
+    """EmbedderEngine::new(contig_data).build_mutual_kgraph(...) (embedder.rs:31-86)"""
+    t = np.ascontiguousarray(tnf, np.float64)
+    c = np.ascontiguousarray(cov, np.float64)
+    dp = C.POINTER(C.c_double)
+    return KGraphResult(load().rh_build_mutual_kgraph(device, t.ctypes.data_as(dp), t.shape[1], c.ctypes.data_as(dp),
+                                                      c.shape[1], t.shape[0], keep_n_edges, n_neighbours, max_layers,
+                                                      ef_construction, int(apply_filters), variant))

@@ -1,0 +1,144 @@
+// capi.cpp — flat C entry points over the C++ host mirror (rosella_host.hpp) so that the Python test-suite can
+// drive it through ctypes.  Test plumbing: the product boundary is include/rosella_gpu.h, and a C++ caller uses
+// rosella_host.hpp directly.  Every function returns 0 / a handle on success and sets rh_last_error() otherwise.
+#include <cstring>
+#include <memory>
+
+#include "rosella_host.hpp"
+
+using namespace rosella;
+
+static thread_local std::string g_err;
+
+template <class F>
+static int guard(F f) {
+    try { f(); return 0; }
+    catch (const std::exception &e) { g_err = e.what(); return -1; }
+    catch (...) { g_err = "unknown C++ exception"; return -1; }
+}
+
+struct rh_graph {
+    KGraph g, tnf;
+    std::vector<size_t> disconnected;
+};
+
+extern "C" {
+
+const char *rh_last_error(void) { return g_err.c_str(); }
+
+int rh_format_f64(double v, char *buf, size_t cap) {
+    return guard([&] {
+        const std::string s = format_f64(v);
+        if (s.size() + 1 > cap) throw Error("rh_format_f64: buffer too small");
+        std::memcpy(buf, s.c_str(), s.size() + 1);
+    });
+}
+
+size_t rh_clamp_n_neighbours(size_t n_included, size_t n_neighbours) { return clamp_n_neighbours(n_included, n_neighbours); }
+
+// ---------------------------------------------------------------- KmerFrequencyTable
+KmerFrequencyTable *rh_table_new(const double *data, size_t nrows, size_t ncols, const char *const *names) {
+    KmerFrequencyTable *t = nullptr;
+    if (guard([&] {
+            auto p = std::make_unique<KmerFrequencyTable>();
+            p->nrows = nrows; p->ncols = ncols;
+            p->kmer_table.assign(data, data + nrows * ncols);
+            for (size_t i = 0; i < nrows; ++i) p->contig_names.emplace_back(names[i]);
+            t = p.release();
+        })) return nullptr;
+    return t;
+}
+void rh_table_free(KmerFrequencyTable *t) { delete t; }
+int rh_table_write(KmerFrequencyTable *t, const char *path) { return guard([&] { t->write(path); }); }
+KmerFrequencyTable *rh_table_read(const char *path, int apply_clr) {
+    KmerFrequencyTable *t = nullptr;
+    if (guard([&] { t = new KmerFrequencyTable(KmerFrequencyTable::read(path, apply_clr != 0)); })) return nullptr;
+    return t;
+}
+size_t rh_table_nrows(const KmerFrequencyTable *t) { return t->nrows; }
+size_t rh_table_ncols(const KmerFrequencyTable *t) { return t->ncols; }
+size_t rh_table_kmer_size(const KmerFrequencyTable *t) { return t->kmer_size; }
+const double *rh_table_data(const KmerFrequencyTable *t) { return t->kmer_table.data(); }
+const char *rh_table_name(const KmerFrequencyTable *t, size_t i) { return t->contig_names.at(i).c_str(); }
+const char *rh_table_path(const KmerFrequencyTable *t) { return t->table_path.c_str(); }
+// returns the number of removed rows, or -1
+long rh_table_filter_by_index(KmerFrequencyTable *t, const size_t *idx, size_t n) {
+    long removed = -1;
+    if (guard([&] { removed = (long)t->filter_by_index(std::set<size_t>(idx, idx + n)).size(); })) return -1;
+    return removed;
+}
+long rh_table_filter_by_name(KmerFrequencyTable *t, const char *const *names, size_t n) {
+    long removed = -1;
+    if (guard([&] {
+            std::set<std::string> s;
+            for (size_t i = 0; i < n; ++i) s.insert(names[i]);
+            removed = (long)t->filter_by_name(s).size();
+        })) return -1;
+    return removed;
+}
+int rh_clr(double *table, size_t nrows, size_t ncols) {
+    return guard([&] {
+        std::vector<double> v(table, table + nrows * ncols);
+        KmerFrequencyTable::clr(v, nrows, ncols);
+        std::copy(v.begin(), v.end(), table);
+    });
+}
+
+// ---------------------------------------------------------------- FASTA / FASTQ
+FastxRecords *rh_fastx_parse(const char *path) {
+    FastxRecords *r = nullptr;
+    if (guard([&] { r = new FastxRecords(parse_fastx_file(path)); })) return nullptr;
+    return r;
+}
+void rh_fastx_free(FastxRecords *r) { delete r; }
+size_t rh_fastx_n(const FastxRecords *r) { return r->ids.size(); }
+const char *rh_fastx_id(const FastxRecords *r, size_t i) { return r->ids.at(i).c_str(); }
+const uint8_t *rh_fastx_seq(const FastxRecords *r) { return r->seq.data(); }
+const uint64_t *rh_fastx_offsets(const FastxRecords *r) { return r->offsets.data(); }
+
+// ---------------------------------------------------------------- GPU entry points of the mirror
+KmerFrequencyTable *rh_count_kmers(int device, const char *assembly, const char *output_directory, int no_flight) {
+    KmerFrequencyTable *t = nullptr;
+    if (guard([&] {
+            Gpu gpu(device);
+            t = new KmerFrequencyTable(count_kmers(gpu, CountKmersArgs{assembly, output_directory}, std::nullopt, no_flight != 0));
+        })) return nullptr;
+    return t;
+}
+
+rh_graph *rh_build_mutual_kgraph(int device, const double *tnf, size_t d, const double *cov, size_t c, size_t n,
+                                 size_t keep_n_edges, size_t n_neighbours, size_t max_layers, size_t ef_construction,
+                                 int apply_filters, uint32_t variant) {
+    rh_graph *out = nullptr;
+    if (guard([&] {
+            Gpu gpu(device);
+            std::vector<std::vector<ContigInformation>> info(n);
+            for (size_t i = 0; i < n; ++i) info[i].push_back(ContigInformation{cov + i * c, c, tnf + i * d, d});
+            EmbedderEngine engine(std::move(info));
+            auto res = engine.build_mutual_kgraph(gpu, keep_n_edges, n_neighbours, n, max_layers, ef_construction,
+                                                  apply_filters != 0, variant);
+            out = new rh_graph{std::move(res.first), engine.last_tnf_kgraph, std::move(res.second)};
+        })) return nullptr;
+    return out;
+}
+void rh_graph_free(rh_graph *g) { delete g; }
+size_t rh_graph_nb_nodes(const rh_graph *g) { return g->g.get_nb_nodes(); }
+size_t rh_graph_max_nbng(const rh_graph *g) { return g->g.get_max_nbng(); }
+size_t rh_graph_n_disconnected(const rh_graph *g) { return g->disconnected.size(); }
+const size_t *rh_graph_disconnected(const rh_graph *g) { return g->disconnected.data(); }
+// which: 0 = the returned kgraph, 1 = the TNF kgraph of the same build
+size_t rh_graph_degree(const rh_graph *g, int which, size_t node) {
+    return (which ? g->tnf : g->g).get_neighbours().at(node).size();
+}
+int rh_graph_neighbours(const rh_graph *g, int which, size_t node, size_t *nodes, double *weights) {
+    return guard([&] {
+        const auto &l = (which ? g->tnf : g->g).get_neighbours().at(node);
+        for (size_t j = 0; j < l.size(); ++j) { nodes[j] = l[j].node; weights[j] = l[j].weight; }
+    });
+}
+long rh_graph_data_id_from_idx(const rh_graph *g, size_t idx) {
+    auto v = g->g.get_data_id_from_idx(idx);
+    return v ? (long)*v : -1;
+}
+
+}  // extern "C"

@@ -123,11 +123,25 @@ KmerFrequencyTable KmerFrequencyTable::read(const std::string &input_file, bool 
     return t;
 }
 
+// ndarray ^0.15 ArrayBase::sum on a contiguous row (numeric_util::unrolled_fold): eight partial sums over strides
+// of 8, folded as acc += (p0+p4), (p1+p5), (p2+p6), (p3+p7), then the < 8 remaining elements in order
+static double ndarray_sum(const double *xs, size_t len) {
+    double p[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc = 0.0;
+    size_t i = 0;
+    for (; i + 8 <= len; i += 8)
+        for (int l = 0; l < 8; ++l) p[l] = p[l] + xs[i + l];
+    acc = acc + (p[0] + p[4]);
+    acc = acc + (p[1] + p[5]);
+    acc = acc + (p[2] + p[6]);
+    acc = acc + (p[3] + p[7]);
+    for (; i < len; ++i) acc = acc + xs[i];
+    return acc;
+}
+
 void KmerFrequencyTable::clr(std::vector<double> &table, size_t nrows, size_t ncols) {
     for (size_t r = 0; r < nrows; ++r) {                                 // :345-355
         double *row = table.data() + r * ncols;
-        double sum = 0.0;
-        for (size_t j = 0; j < ncols; ++j) sum += row[j];
+        const double sum = ndarray_sum(row, ncols);                      // row.sum(), :345
         const double mean = sum / (double)ncols;
         for (size_t j = 0; j < ncols; ++j) row[j] = std::log(row[j] / mean);
     }

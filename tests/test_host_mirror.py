@@ -1,0 +1,221 @@
+"""The C++ host mirror of the reference's Rust interface (rosella_b200/host/rosella_host.hpp) — CPU tests of the
+table type, CSV round trip, CLR, filters and the FASTA reader; GPU tests of count_kmers and
+EmbedderEngine::build_mutual_kgraph against the oracle.  Reference lines are cited per test."""
+import gzip
+import math
+import os
+import random
+import struct
+
+import numpy as np
+import pytest
+
+import oracle
+from rosella_b200 import host, synth
+
+
+def _ryu_pretty(v: float) -> str:
+    """Independent model of the text Rust's csv crate writes for an f64 (ryu pretty format)."""
+    if math.isnan(v):
+        return "NaN"
+    if math.isinf(v):
+        return "-inf" if v < 0 else "inf"
+    sign = "-" if math.copysign(1.0, v) < 0 else ""
+    if v == 0:
+        return sign + "0.0"
+    mant, exp = f"{abs(v):.17e}".split("e")           # exact enough to recover repr's digits below
+    r = repr(abs(v))
+    if "e" in r:
+        m, e = r.split("e"); e = int(e)
+    else:
+        m, e = r, 0
+    if "." in m:
+        ip, fp = m.split(".")
+    else:
+        ip, fp = m, ""
+    digits = (ip + fp).lstrip("0")
+    k = e - len(fp)                                    # value = digits * 10^k
+    stripped = digits.rstrip("0")
+    k += len(digits) - len(stripped)
+    digits = stripped or "0"
+    n = len(digits)
+    kk = n + k
+    if 0 <= k and kk <= 16:
+        return sign + digits + "0" * k + ".0"
+    if 0 < kk <= 16:
+        return sign + digits[:kk] + "." + digits[kk:]
+    if -5 < kk <= 0:
+        return sign + "0." + "0" * (-kk) + digits
+    if n == 1:
+        return sign + digits + "e" + str(kk - 1)
+    return sign + digits[0] + "." + digits[1:] + "e" + str(kk - 1)
+
+
+def test_format_f64_is_shortest_round_trip_in_ryu_layout():
+    known = {1.0: "1.0", 0.1: "0.1", 0.3: "0.3", 1e-5: "0.00001", 1e-6: "1e-6", 1e16: "1e16", 1e15: "1000000000000000.0",
+             1.5e300: "1.5e300", 123456789.125: "123456789.125", 1.2345678901234568e17: "1.2345678901234568e17",
+             5e-324: "5e-324", -2.5: "-2.5", 0.0: "0.0", float("nan"): "NaN", float("inf"): "inf", float("-inf"): "-inf",
+             0.007352941176470588: "0.007352941176470588"}
+    for v, want in known.items():
+        assert host.format_f64(v) == want, (v, host.format_f64(v), want)
+    rng = random.Random(7)
+    for _ in range(3000):
+        v = struct.unpack("<d", struct.pack("<Q", rng.getrandbits(64)))[0]
+        if math.isnan(v) or math.isinf(v):
+            continue
+        s = host.format_f64(v)
+        assert float(s) == v and s == _ryu_pretty(v), (v, s, _ryu_pretty(v))
+    for v in np.random.default_rng(1).dirichlet(np.ones(136)):      # the values the table really holds
+        s = host.format_f64(float(v))
+        assert float(s) == v and s == _ryu_pretty(float(v))
+
+
+def test_table_write_read_round_trip_is_bit_exact(tmp_path):
+    """KmerFrequencyTable::write / read (kmer_counting.rs:285-333): header-less CSV, f64 text round trip."""
+    rng = np.random.default_rng(2)
+    counts = rng.integers(0, 500, (40, 136)).astype(np.float64)
+    counts[3] = 0.0                                                  # 0/0 row -> NaN (:104-107)
+    with np.errstate(invalid="ignore"):
+        freq = counts / counts.sum(axis=1, keepdims=True)
+    names = [f"contig_{i} len={i * 7}" for i in range(39)] + ['odd,"name"']
+    t = host.KmerFrequencyTable.new(freq, names)
+    path = str(tmp_path / "kmer_frequencies.tsv")
+    t.write(path)
+    assert t.table_path == path
+    first = open(path).readline().rstrip("\n").split(",")
+    assert first[0] == names[0] and len(first) == 137                # no header, comma separated (:287-291)
+    back = host.KmerFrequencyTable.read(path)
+    assert back.contig_names == names and back.kmer_size == 4
+    assert np.array_equal(back.kmer_table, freq, equal_nan=True)
+    clr = host.KmerFrequencyTable.read(path, apply_clr=True).kmer_table        # the no_flight feature (:322-323)
+    assert np.array_equal(clr, oracle.clr(freq), equal_nan=True)
+    with pytest.raises(host.HostError):
+        host.KmerFrequencyTable.read(str(tmp_path / "missing.tsv"))
+    bad = tmp_path / "bad.tsv"
+    bad.write_text("a,0.5,zzz\n")
+    with pytest.raises(host.HostError, match="invalid float"):
+        host.KmerFrequencyTable.read(str(bad))
+
+
+def test_table_filters(tmp_path):
+    """filter_by_index / filter_by_name (kmer_counting.rs:228-282)"""
+    x = np.arange(12 * 136, dtype=np.float64).reshape(12, 136)
+    names = [f"c{i}" for i in range(12)]
+    t = host.KmerFrequencyTable.new(x, names)
+    assert t.filter_by_index([1, 5, 11]) == 3
+    keep = [i for i in range(12) if i not in (1, 5, 11)]
+    assert t.contig_names == [names[i] for i in keep] and np.array_equal(t.kmer_table, x[keep])
+    assert t.filter_by_name(["c0", "c7", "nope"]) == 2
+    keep = [i for i in keep if i not in (0, 7)]
+    assert t.contig_names == [names[i] for i in keep] and np.array_equal(t.kmer_table, x[keep])
+    with pytest.raises(host.HostError, match="out of range"):
+        t.filter_by_index([100])
+
+
+def test_clr_and_k_clamp():
+    x = np.random.default_rng(4).dirichlet(np.ones(136), 9)
+    x = np.concatenate([x, x[:, :131] * 1.5], axis=1)[:, :131 + 136]    # a width that is not a multiple of 8
+    # :345-355 with row.sum() in ndarray's order: 8 strided partial sums, (p0+p4)+(p1+p5)+(p2+p6)+(p3+p7), remainder
+    def nd_sum(r):
+        m = len(r) // 8 * 8
+        p = [0.0] * 8
+        for i in range(0, m, 8):
+            for l in range(8):
+                p[l] = p[l] + r[i + l]
+        acc = 0.0
+        for a, b in ((0, 4), (1, 5), (2, 6), (3, 7)):
+            acc = acc + (p[a] + p[b])
+        for v in r[m:]:
+            acc = acc + v
+        return acc
+    want = np.array([[math.log(v / (nd_sum(r.tolist()) / len(r))) for v in r.tolist()] for r in x])
+    assert np.array_equal(host.clr(x), want) and np.array_equal(oracle.clr(x), want)
+    # recover_engine.rs:513-517
+    assert host.clamp_n_neighbours(50, 30) == 25 and host.clamp_n_neighbours(299, 30) == 30
+    assert host.clamp_n_neighbours(300, 30) == 30 and host.clamp_n_neighbours(10, 30) == 5
+
+
+def _write_fasta(path, ids, seqs, width=60, gz=False):
+    text = "".join(f">{i}\n" + "".join(s[p:p + width] + "\n" for p in range(0, len(s), width)) for i, s in zip(ids, seqs))
+    if gz:
+        with gzip.open(path, "wt") as f:
+            f.write(text)
+    else:
+        open(path, "w").write(text)
+
+
+def test_parse_fastx_file(tmp_path):
+    rng = np.random.default_rng(5)
+    ids = ["k141_1 flag=1 multi=3.0 len=300", "k141_2", "empty"]
+    seqs = ["".join(rng.choice(list("ACGTNacgt"), 300)), "".join(rng.choice(list("ACGT"), 61)), ""]
+    for gz in (False, True):
+        p = str(tmp_path / ("a.fna.gz" if gz else "a.fna"))
+        _write_fasta(p, ids, seqs, gz=gz)
+        got_ids, seq, offs = host.parse_fastx_file(p)
+        assert got_ids == ids and len(offs) == 4
+        for i, s in enumerate(seqs):
+            raw = bytes(seq[int(offs[i]):int(offs[i + 1])])
+            assert oracle.normalize(raw).decode() == oracle.normalize(s.encode()).decode()
+    fq = tmp_path / "r.fq"
+    fq.write_text("@r1\nACGT\n+\nIIII\n@r2 x\nGGCC\n+\nIIII\n")
+    got_ids, seq, offs = host.parse_fastx_file(str(fq))
+    assert got_ids == ["r1", "r2 x"] and bytes(seq) == b"ACGTGGCC" and list(offs) == [0, 4, 8]
+    with pytest.raises(host.HostError):
+        host.parse_fastx_file(str(tmp_path / "missing.fna"))
+    junk = tmp_path / "junk.txt"
+    junk.write_text("hello\n")
+    with pytest.raises(host.HostError, match="invalid start"):
+        host.parse_fastx_file(str(junk))
+
+
+@pytest.mark.gpu
+def test_count_kmers_matches_the_oracle_and_reuses_the_table(tmp_path):
+    """count_kmers (kmer_counting.rs:13-16, :41-123): FASTA -> GPU counts -> kmer_frequencies.tsv -> re-read."""
+    seq, offs = synth.contigs(400_000, threads=2)
+    ids = [f"contig_{i}" for i in range(len(offs) - 1)]
+    seqs = [bytes(seq[int(offs[i]):int(offs[i + 1])]).decode() for i in range(len(ids))]
+    fa = str(tmp_path / "assembly.fna")
+    _write_fasta(fa, ids, seqs)
+    out = str(tmp_path / "out")
+    os.makedirs(out)
+    t = host.count_kmers(fa, out)
+    _, _, want = oracle.tnf_count(seq, offs, fast=True)
+    assert t.contig_names == ids and np.array_equal(t.kmer_table, want, equal_nan=True)
+    assert t.table_path == os.path.join(out, "kmer_frequencies.tsv") and os.path.exists(t.table_path)
+    # second call reads the existing table (:46-50), with the no_flight CLR applied on read (:322-323)
+    os.remove(fa)
+    t2 = host.count_kmers(fa, out, no_flight=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        assert np.array_equal(t2.kmer_table, oracle.clr(want), equal_nan=True)
+
+
+@pytest.mark.gpu
+def test_build_mutual_kgraph_matches_the_exhaustive_oracle():
+    """EmbedderEngine::build_mutual_kgraph (embedder.rs:31-86): the returned graph is the depth kNN graph (the
+    reference drops the intersect / mutual results, nearest_neighbour_graph.rs:33,:70); apply_filters applies them."""
+    n, s, k = 900, 5, 20
+    tnf, cov, _ = synth.knn_tables(n, s, seed=17)
+    g = host.build_mutual_kgraph(tnf, cov, keep_n_edges=3, n_neighbours=k)
+    assert g.nb_nodes == n and g.max_nbng == k and g.disconnected_nodes == [] and g.data_id_from_idx(7) == 7
+    di, dd, _ = oracle.knn(cov, oracle.DEPTH, k)
+    ti, td, _ = oracle.knn(tnf, oracle.TNF, k)
+    agree = 0
+    for node in range(n):
+        nodes, w = g.neighbours(node)
+        tn, tw = g.neighbours(node, tnf=True)
+        assert len(nodes) == k and (np.diff(w) >= 0).all()
+        agree += int(np.array_equal(nodes, di[node])) + int(np.array_equal(tn, ti[node]))
+        m = nodes == di[node]
+        assert np.allclose(w[m], dd[node][m].astype(np.float64), rtol=2.4e-7, atol=0)
+    assert agree > 0.97 * 2 * n
+    # filters applied: keep the first max(keep_n_edges, 5) edges of the depth list, then only edges whose reverse
+    # is in the TNF graph (embedder.rs:68), then the same with mutual edges and keep_n_edges (:69)
+    f = host.build_mutual_kgraph(tnf, cov, keep_n_edges=3, n_neighbours=k, apply_filters=True)
+    lists = [g.neighbours(i)[0] for i in range(n)]
+    tl = [set(g.neighbours(i, tnf=True)[0].tolist()) for i in range(n)]
+    step1 = [[int(nb) for j, nb in enumerate(l) if j < 5 or i in tl[int(nb)]] for i, l in enumerate(lists)]
+    s1 = [set(l) for l in step1]
+    step2 = [[nb for j, nb in enumerate(l) if j < 3 or i in s1[nb]] for i, l in enumerate(step1)]
+    for i in range(n):
+        assert f.neighbours(i)[0].tolist() == step2[i]
+    assert f.disconnected_nodes == [i for i in range(n) if not step2[i]]
