@@ -10,6 +10,8 @@
 //     - the equal-variance branch is blended arithmetically (r = 0 and a signed half-difference
 //       he select it) instead of four FSELs, sqrt takes |q| as a source modifier, and the
 //       accumulators are updated by predicated FADDs instead of FSEL + FADD.
+#include <algorithm>
+
 #include "pk.cuh"
 #include "rg_internal.cuh"
 
@@ -99,16 +101,18 @@ constexpr int WARPS = 8;
 constexpr int QB = QPW * WARPS; // 32 query rows per CTA
 constexpr int PAIRS = QB / 2;
 
-// Shared memory: 2 reference stages [S][32] float4 | query pairs [S][PAIRS] 2 x float4
-// ({x0,x1,y0,y1},{z0,z1,w0,w1}) | K' lists | 2 mbarriers
+// Shared memory: 2 reference stages [SC][32] float4 | query pairs [S][PAIRS] 2 x float4
+// ({x0,x1,y0,y1},{z0,z1,w0,w1}) | K' lists | 2 mbarriers.  A stage holds SC <= S consecutive samples of one 32-row
+// reference tile (contiguous in cov_t), so the ring stays small when S is large and two CTAs still fit per SM;
+// the per-row accumulators live in registers across the chunks of a tile.
 template <int VARIANT, int K>
 __global__ void __launch_bounds__(WARPS * 32, 2)
-depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, uint32_t n_tiles, uint32_t q_begin,
-                     uint32_t q_count, float *__restrict__ cand_d, uint32_t *__restrict__ cand_i) {
+depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, uint32_t SC, uint32_t n_tiles,
+                     uint32_t q_begin, uint32_t q_count, float *__restrict__ cand_d, uint32_t *__restrict__ cand_i) {
     extern __shared__ __align__(128) uint8_t smem[];
-    const uint32_t tile_f4 = S * RG_TILE;
-    float4 *stage[2] = {reinterpret_cast<float4 *>(smem), reinterpret_cast<float4 *>(smem) + tile_f4};
-    float *qd = reinterpret_cast<float *>(stage[1] + tile_f4);
+    const uint32_t tile_f4 = S * RG_TILE, stage_f4 = SC * RG_TILE;
+    float4 *stage[2] = {reinterpret_cast<float4 *>(smem), reinterpret_cast<float4 *>(smem) + stage_f4};
+    float *qd = reinterpret_cast<float *>(stage[1] + stage_f4);
     float *list_d = qd + tile_f4 * 4;
     uint32_t *list_i = reinterpret_cast<uint32_t *>(list_d + QB * K);
     uint64_t *bars = reinterpret_cast<uint64_t *>(list_i + QB * K);
@@ -134,11 +138,18 @@ depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, u
         mbar_fence_init();
     }
     __syncthreads();
-    const uint32_t tile_bytes = tile_f4 * sizeof(float4);
-    if (tid == 0) {
-        mbar_expect_tx(&bars[0], tile_bytes);
-        tma_bulk_g2s(stage[0], cov_t, tile_bytes, &bars[0]);
-    }
+    const uint32_t n_chunks = (S + SC - 1) / SC;
+    const uint32_t n_stages = n_tiles * n_chunks;
+    // stage g = (tile g / n_chunks, samples [c * SC, min(S, (c + 1) * SC)) with c = g % n_chunks)
+    auto issue = [&](uint32_t g) {
+        const uint32_t t = g / n_chunks, c = g - t * n_chunks;
+        const uint32_t len = min(SC, S - c * SC);
+        const uint32_t bytes = len * RG_TILE * (uint32_t)sizeof(float4);
+        uint64_t *bar = &bars[g & 1];
+        mbar_expect_tx(bar, bytes);
+        tma_bulk_g2s(stage[g & 1], cov_t + ((uint64_t)t * S + (uint64_t)c * SC) * RG_TILE, bytes, bar);
+    };
+    if (tid == 0) issue(0);
     float thr[QPW];
     uint32_t qrow[QPW];
 #pragma unroll
@@ -148,34 +159,38 @@ depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, u
     }
     const ulonglong2 *qp = reinterpret_cast<const ulonglong2 *>(qd) + warp * 4;   // 2 pairs x 2 ulonglong2
 
-    for (uint32_t t = 0; t < n_tiles; ++t) {
-        __syncthreads();   // every warp is done with tile t-1, so its stage may be overwritten
-        if (tid == 0 && t + 1 < n_tiles) {
-            uint64_t *bar = &bars[(t + 1) & 1];
-            mbar_expect_tx(bar, tile_bytes);
-            tma_bulk_g2s(stage[(t + 1) & 1], cov_t + (uint64_t)(t + 1) * tile_f4, tile_bytes, bar);
-        }
-        mbar_wait(&bars[t & 1], (t >> 1) & 1);
-        const float4 *ref = stage[t & 1];
-        float acc[QPW], cnt[QPW];
+    float acc[QPW], cnt[QPW];
 #pragma unroll
-        for (int u = 0; u < QPW; ++u) acc[u] = cnt[u] = 0.f;
+    for (int u = 0; u < QPW; ++u) acc[u] = cnt[u] = 0.f;
+    uint32_t t = 0, c = 0;
+    for (uint32_t g = 0; g < n_stages; ++g) {
+        __syncthreads();   // every warp is done with stage g-1, so its buffer may be overwritten
+        if (tid == 0 && g + 1 < n_stages) issue(g + 1);
+        mbar_wait(&bars[g & 1], (g >> 1) & 1);
+        const float4 *ref = stage[g & 1];
+        const uint32_t s0 = c * SC, len = min(SC, S - s0);
+        const ulonglong2 *qs = qp + (size_t)s0 * (PAIRS * 2);
 #pragma unroll 2
-        for (uint32_t s = 0; s < S; ++s) {
+        for (uint32_t s = 0; s < len; ++s) {
             const float4 b = ref[s * RG_TILE + lane];
 #pragma unroll
             for (int pr = 0; pr < 2; ++pr) {
-                const ulonglong2 xy = qp[s * (PAIRS * 2) + pr * 2], zw = qp[s * (PAIRS * 2) + pr * 2 + 1];
+                const ulonglong2 xy = qs[s * (PAIRS * 2) + pr * 2], zw = qs[s * (PAIRS * 2) + pr * 2 + 1];
                 depth_sample2<VARIANT>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc[2 * pr], cnt[2 * pr],
                                        acc[2 * pr + 1], cnt[2 * pr + 1]);
             }
         }
-        const uint32_t ridx = t * RG_TILE + lane;
+        if (++c == n_chunks) {          // last chunk of tile t: finish the 4 x 32 distances and offer them
+            const uint32_t ridx = t * RG_TILE + lane;
 #pragma unroll
-        for (int u = 0; u < QPW; ++u) {
-            float d = depth_finish<VARIANT>(acc[u], cnt[u]);
-            if (ridx >= n || ridx == qrow[u] || qrow[u] >= q_end) d = INFINITY;
-            topk_offer<K>(list_d + (warp * QPW + u) * K, list_i + (warp * QPW + u) * K, d, ridx, thr[u], lane);
+            for (int u = 0; u < QPW; ++u) {
+                float d = depth_finish<VARIANT>(acc[u], cnt[u]);
+                if (ridx >= n || ridx == qrow[u] || qrow[u] >= q_end) d = INFINITY;
+                topk_offer<K>(list_d + (warp * QPW + u) * K, list_i + (warp * QPW + u) * K, d, ridx, thr[u], lane);
+                acc[u] = cnt[u] = 0.f;
+            }
+            c = 0;
+            ++t;
         }
     }
     __syncwarp();
@@ -191,18 +206,37 @@ depth_select2_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, u
     }
 }
 
+// samples per stage: the largest chunk that still lets two CTAs share an SM, else the largest that fits at all
+static uint32_t pick_chunk(uint32_t S, size_t fixed_bytes, size_t &smem) {
+    const size_t per_sample = (size_t)RG_TILE * sizeof(float4);             // 512 B per sample per stage
+    const size_t budgets[2] = {(size_t)113 * 1024, (size_t)227 * 1024};     // 2 CTAs / SM, 1 CTA / SM
+    for (size_t budget : budgets) {
+        if (fixed_bytes + 2 * per_sample > budget) continue;
+        uint32_t sc = (uint32_t)std::min<size_t>(S, (budget - fixed_bytes) / (2 * per_sample));
+        if (sc < S && sc < 8 && budget == budgets[0]) continue;             // tiny stages: one CTA per SM is better
+        // even out the chunks (e.g. S = 100, max 30 -> 4 chunks of 25)
+        const uint32_t chunks = (S + sc - 1) / sc;
+        sc = (S + chunks - 1) / chunks;
+        smem = fixed_bytes + 2 * per_sample * sc;
+        return sc;
+    }
+    return 0;
+}
+
 template <int VARIANT, int K>
 int32_t launch(rg_handle *h, uint64_t q_begin, uint64_t q_count) {
     const size_t tile_bytes = (size_t)h->s * RG_TILE * sizeof(float4);
-    const size_t smem = 3 * tile_bytes + (size_t)QB * K * 8 + 2 * sizeof(uint64_t);
-    if (smem > 227 * 1024)
+    const size_t fixed = tile_bytes + (size_t)QB * K * 8 + 2 * sizeof(uint64_t);   // query pairs + lists + barriers
+    size_t smem = 0;
+    const uint32_t sc = pick_chunk(h->s, fixed, smem);
+    if (sc == 0)
         return rg_fail(h, RG_ERR_INVALID,
-                       "depth select: %u samples with K'=%d need %zu bytes of shared memory (> 227 KB); "
-                       "at most ~128 samples are supported in this version", h->s, K, smem);
+                       "depth select: %u samples with K'=%d need %zu bytes of shared memory for the query rows and "
+                       "lists alone (> 227 KB)", h->s, K, fixed);
     auto kern = depth_select2_kernel<VARIANT, K>;
     RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = (unsigned)((q_count + QB - 1) / QB);
-    kern<<<grid, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, (uint32_t)h->n, h->s,
+    kern<<<grid, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, (uint32_t)h->n, h->s, sc,
                                                 (uint32_t)h->n_tiles, (uint32_t)q_begin, (uint32_t)q_count,
                                                 (float *)h->cand_d.p, (uint32_t *)h->cand_i.p);
     RG_CUDA(h, cudaGetLastError());

@@ -131,6 +131,20 @@ def test_knn_k_range(ctx, k, n):
     check_against_oracle(cov, oracle.DEPTH, oracle.RUST, k, di, dd)
 
 
+@pytest.mark.parametrize("n,s,k", [(700, 100, 50), (500, 131, 30), (300, 230, 10), (200, 400, 5)])
+def test_knn_many_samples(ctx, n, s, k):
+    """BASELINE.json configs[4] shape (100 samples, k = 50) and beyond: the depth kernel stages a reference tile
+    in chunks of samples (4 x 25, 3 x 44, 2 x 115, 80 x 5 here) and carries the accumulators across them."""
+    tnf, cov, _ = synth.knn_tables(n, s, seed=40 + s)
+    ctx.knn_load(None, cov, gpu.VARIANT_RUST)
+    di, dd, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    check_against_oracle(cov, oracle.DEPTH, oracle.RUST, k, di, dd)
+    if s == 100:
+        ctx.knn_load(None, cov, gpu.VARIANT_FLIGHT)
+        di, dd, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+        check_against_oracle(cov, oracle.DEPTH, oracle.FLIGHT, k, di, dd)
+
+
 def test_knn_fewer_rows_than_k(ctx):
     tnf, cov, _ = synth.knn_tables(10, 2, seed=3)
     (ti, td), (di, dd) = ctx.knn_build(tnf, cov, 30)
