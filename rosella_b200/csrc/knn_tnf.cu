@@ -8,6 +8,9 @@
 // tensor cores for this term only if shown within tolerance; FP32 CUDA cores are used and the term
 // is <= 4% of the path's flops at the headline shape, see DESIGN.md §4.3.
 // Selection only — knn_rescore.cu recomputes the kept candidates in f64.
+#include <cstdlib>
+
+#include "knn_tnf_common.cuh"
 #include "rg_internal.cuh"
 
 namespace {
@@ -15,30 +18,6 @@ namespace {
 constexpr int QPW = 8;
 constexpr int WARPS = 8;
 constexpr int QB = QPW * WARPS;   // 64 query rows per CTA
-
-// VARIANT 2 = squared Euclidean distance of the rows as passed (RG_GRAPH_TNF_EUCLID; flight/flight/metrics.py:64-77):
-// |x - y|^2 = |x~|^2 + |y~|^2 - 2 x~.y~ + d (mean_x - mean_y)^2 on the centred rows; selection only needs the order,
-// so the square root is left to the f64 re-evaluation.
-constexpr int METRIC_EUCLID = 2;
-
-template <int VARIANT>
-__device__ __forceinline__ float tnf_finish(float dot, float nq, float nr, float dmu2) {
-    const float den = nq + nr;                      // NaN when either row is flagged non-finite
-    float d;
-    if (VARIANT == METRIC_EUCLID) {
-        d = fmaxf(fmaf(-2.0f, dot, den) + dmu2, 0.f);
-        if (den != den) d = 3.402823466e+38f;       // non-finite row: the defined maximum (include/rosella_gpu.h)
-    } else if (VARIANT == RG_VARIANT_RUST) {
-        d = 0.5f - __fdividef(dot, den);
-        if (dot == 0.f) d = 1.0f;                   // :385
-        if (nq == 0.f && nr == 0.f) d = 0.f;        // :383
-        if (d != d) d = 1.0f;                       // :410
-    } else {
-        d = 1.0f - 2.0f * __fdividef(dot, den);
-        if (d != d) d = 2.0f;                       // defined here as the metric's maximum (include/rosella_gpu.h)
-    }
-    return d;
-}
 
 template <int VARIANT, int K, int RR>
 __global__ void __launch_bounds__(WARPS * 32, 1)
@@ -183,7 +162,15 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 
 }  // namespace
 
+bool rg_tnf_select_tc_supported(const rg_handle *h, uint32_t kprime);
+int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint64_t q_begin, uint64_t q_count);
+
+// The tcgen05 kernel (knn_tnf_tc.cu) is the product path wherever its shape limits allow (K' = 64, d % 8 == 0);
+// larger K' lists do not fit in registers and take the FP32 CUDA-core kernel below.  RG_TNF_SELECT_IMPL=fp32
+// forces the CUDA-core kernel for A/B measurements.
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    static const bool force_fp32 = [] { const char *e = getenv("RG_TNF_SELECT_IMPL"); return e && e[0] == 'f'; }();
+    if (!force_fp32 && rg_tnf_select_tc_supported(h, kprime)) return rg_launch_tnf_select_tc(h, which, q_begin, q_count);
     if (which == RG_GRAPH_TNF_EUCLID) return launch_k<METRIC_EUCLID>(h, kprime, q_begin, q_count);
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);

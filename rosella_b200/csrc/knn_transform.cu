@@ -3,18 +3,32 @@
 //
 // Device layouts (RG_TILE = 32 rows per tile, one row per lane):
 //   tnf_t  float4 [n_tiles][d/4][32]   centred rows x - mean(x)  (kmer_counting.rs:367-377)
+//   tnf_hi / tnf_lo  float4 [n_panels][d/4][128]: the same centred rows split as x = hi + lo with hi = tf32(x),
+//                                      lo = tf32(x - hi), in 128-row panels.  Inside a panel every 16-byte K slice
+//                                      holds its 128 rows contiguously, i.e. 8-row x 16-byte core matrices 128 B
+//                                      apart along M/N and 2048 B apart along K: the K-major no-swizzle canonical
+//                                      layout tcgen05.mma reads through a shared-memory descriptor (knn_tnf_tc.cu)
 //   cov_t  float4 [n_tiles][s][32]     (mean+eps, max(var+eps,1), ln var', +-1/(sqrt(var')*sqrt2))
 //                                      sign of .w = "mean+eps > eps" (coverage_calculator.rs:600-619)
 // Each tile is one contiguous block so a single TMA bulk copy stages it into shared memory, and
 // for a fixed (j/4 or sample) the 32 lanes read 32 consecutive float4 (conflict-free LDS.128).
 #include "rg_internal.cuh"
 
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
 __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n, uint32_t d,
-                                     float *__restrict__ out, float *__restrict__ norm, float *__restrict__ mean) {
+                                     float *__restrict__ out, float *__restrict__ norm, float *__restrict__ mean,
+                                     float *__restrict__ hi, float *__restrict__ lo) {
     const int lane = threadIdx.x & 31;
     const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const uint64_t rows_padded = (n + RG_TILE - 1) / RG_TILE * RG_TILE;
+    const uint64_t rows_padded = (n + RG_PANEL - 1) / RG_PANEL * RG_PANEL;
     if (row >= rows_padded) return;
+    const uint64_t panel = row / RG_PANEL;
+    const uint32_t pr = (uint32_t)(row % RG_PANEL);
     const uint64_t tile = row / RG_TILE;
     const uint32_t r = (uint32_t)(row % RG_TILE);
     double x[8];
@@ -38,7 +52,12 @@ __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n,
             double c = row < n ? x[it] - mu : 0.0;
             if (!isfinite(c)) { bad = 1; c = 0.0; }
             nn += c * c;
-            out[((tile * (d / 4) + j / 4) * RG_TILE + r) * 4 + (j & 3)] = (float)c;
+            const float cf = (float)c;
+            out[((tile * (d / 4) + j / 4) * RG_TILE + r) * 4 + (j & 3)] = cf;
+            const float h = to_tf32(cf);
+            const uint64_t o = ((panel * (d / 4) + j / 4) * RG_PANEL + pr) * 4 + (j & 3);
+            hi[o] = h;
+            lo[o] = to_tf32(cf - h);
         }
     }
 #pragma unroll
@@ -93,7 +112,8 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     h->n = 0;
     h->has_tnf = h->has_cov = false;
     const uint64_t n_tiles = (n + RG_TILE - 1) / RG_TILE;
-    const uint64_t rows_padded = n_tiles * RG_TILE;
+    const uint64_t n_panels = (n + RG_PANEL - 1) / RG_PANEL;
+    const uint64_t rows_padded = n_panels * RG_PANEL;   // whole 128-row panels (a multiple of the 32-row tiles)
     RG_TRY(rg_reserve(h, h->err_flag, sizeof(uint32_t)));
     RG_CUDA(h, cudaMemsetAsync(h->err_flag.p, 0, sizeof(uint32_t), h->stream));
 
@@ -103,6 +123,8 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
         RG_TRY(rg_reserve(h, h->tnf_t, rows_padded * d * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_norm, rows_padded * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_mean, rows_padded * sizeof(float)));
+        RG_TRY(rg_reserve(h, h->tnf_hi, rows_padded * d * sizeof(float)));
+        RG_TRY(rg_reserve(h, h->tnf_lo, rows_padded * d * sizeof(float)));
         RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         h->tm.h2d_bytes += n * d * sizeof(double);
     }
@@ -116,7 +138,8 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     if (tnf) {
         const int wpb = 8;
         tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
-            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p);
+            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p,
+            (float *)h->tnf_hi.p, (float *)h->tnf_lo.p);
         RG_CUDA(h, cudaGetLastError());
         h->tm.kernel_launches += 1;
     }
@@ -140,7 +163,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
         return rg_fail(h, RG_ERR_INVALID,
                        "rg_knn_load: coverage table holds a non-finite value (the reference panics in "
                        "Normal::new, coverage_calculator.rs:639)");
-    h->n = n; h->d = d; h->s = s; h->variant = variant; h->n_tiles = n_tiles;
+    h->n = n; h->d = d; h->s = s; h->variant = variant; h->n_tiles = n_tiles; h->n_panels = n_panels;
     h->has_tnf = tnf != nullptr;
     h->has_cov = cov != nullptr;
     return RG_OK;

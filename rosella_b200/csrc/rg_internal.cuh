@@ -11,6 +11,7 @@
 #include "../../include/rosella_gpu.h"
 
 #define RG_TILE 32u   // rows per tile of the tile-major device layouts (one row per lane)
+#define RG_PANEL 128u // rows per panel of the tensor-core operand layout (UMMA M = N = 128)
 
 struct DevBuf {
     void *p = nullptr;
@@ -34,6 +35,8 @@ struct rg_handle {
     DevBuf tnf_t;             // f32 centred rows, tile-major [tile][d/4][32] float4
     DevBuf tnf_norm;          // f32 [n_tiles*32] sum of squares of the centred row (NaN = non-finite row)
     DevBuf tnf_mean;          // f32 [n_tiles*32] mean of the row as passed (Euclidean graph)
+    DevBuf tnf_hi, tnf_lo;    // tf32 split of the centred rows, panel-major [panels][d/4][128] float4 (tensor-core select)
+    uint64_t n_panels = 0;    // 128-row panels
     DevBuf cov_t;             // float4 (mean, var, ln var, +-1/(sd*sqrt2)) tile-major [tile][s][32]
     DevBuf err_flag;          // u32 device error word (non-finite coverage, ...)
     DevBuf cand_d, cand_i;    // select-phase candidates [rows][kprime]
