@@ -194,6 +194,7 @@ int32_t launch_rescore(rg_handle *h, const double *data, uint32_t width, uint32_
 
 int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
+uint32_t rg_tnf_kprime(const rg_handle *h, uint32_t k, uint32_t general);
 
 // K' = candidates kept by the FP32 select phase: k plus a margin that absorbs FP32 reordering
 static uint32_t pick_kprime(uint32_t k) {
@@ -214,7 +215,8 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
     if (q_begin > q_end || q_end > h->n)
         return rg_fail(h, RG_ERR_INVALID, "rg_knn_search: query range [%llu,%llu) outside [0,%llu)",
                        (unsigned long long)q_begin, (unsigned long long)q_end, (unsigned long long)h->n);
-    const uint32_t kprime = pick_kprime(k);
+    uint32_t kprime = pick_kprime(k);
+    if (kprime && which != RG_GRAPH_DEPTH) kprime = rg_tnf_kprime(h, k, kprime);
     if (k == 0 || kprime == 0) return rg_fail(h, RG_ERR_INVALID, "rg_knn_search: k=%u must be in [1,224]", k);
     const uint64_t q_count = q_end - q_begin;
     if (q_count == 0) return RG_OK;

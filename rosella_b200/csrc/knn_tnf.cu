@@ -163,14 +163,25 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 }  // namespace
 
 bool rg_tnf_select_tc_supported(const rg_handle *h, uint32_t kprime);
-int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint64_t q_begin, uint64_t q_count);
+int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 
 // The tcgen05 kernel (knn_tnf_tc.cu) is the product path wherever its shape limits allow (K' = 64, d % 8 == 0);
 // larger K' lists do not fit in registers and take the FP32 CUDA-core kernel below.  RG_TNF_SELECT_IMPL=fp32
 // forces the CUDA-core kernel for A/B measurements.
+static bool force_fp32() {
+    static const bool f = [] { const char *e = getenv("RG_TNF_SELECT_IMPL"); return e && e[0] == 'f'; }();
+    return f;
+}
+
+// K' of the TNF graphs: the tensor-core kernel evaluates the dot product to FP32 accuracy (3xTF32), so k <= 32
+// needs no more than 48 candidates; everything else keeps the general K' (knn_rescore.cu: pick_kprime)
+uint32_t rg_tnf_kprime(const rg_handle *h, uint32_t k, uint32_t general) {
+    if (k <= 32 && !force_fp32() && rg_tnf_select_tc_supported(h, 48)) return 48;
+    return general;
+}
+
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
-    static const bool force_fp32 = [] { const char *e = getenv("RG_TNF_SELECT_IMPL"); return e && e[0] == 'f'; }();
-    if (!force_fp32 && rg_tnf_select_tc_supported(h, kprime)) return rg_launch_tnf_select_tc(h, which, q_begin, q_count);
+    if (!force_fp32() && rg_tnf_select_tc_supported(h, kprime)) return rg_launch_tnf_select_tc(h, which, kprime, q_begin, q_count);
     if (which == RG_GRAPH_TNF_EUCLID) return launch_k<METRIC_EUCLID>(h, kprime, q_begin, q_count);
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);

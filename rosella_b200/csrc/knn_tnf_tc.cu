@@ -105,11 +105,11 @@ __device__ __forceinline__ float tmem_ld1(uint32_t taddr) {
 // ---------------------------------------------------------------- per-thread sorted list in registers
 // ld ascending; a new entry goes AFTER equal ones (candidates arrive in increasing index order, so ties stay
 // ordered by index).  Fully unrolled compare-exchange chain: no dynamic register indexing.
-template <int K>
-__device__ __forceinline__ void list_insert(float (&ld)[K], uint32_t (&li)[K], float d, uint32_t idx) {
+template <int K, int START>
+__device__ __forceinline__ void list_insert_from(float (&ld)[K], uint32_t (&li)[K], float d, uint32_t idx) {
     bool p = false;
 #pragma unroll
-    for (int e = 0; e < K; ++e) {
+    for (int e = START; e < K; ++e) {
         p = p || d < ld[e];                  // once displaced, everything behind moves down by one
         const float td = ld[e];
         const uint32_t ti = li[e];
@@ -118,6 +118,16 @@ __device__ __forceinline__ void list_insert(float (&ld)[K], uint32_t (&li)[K], f
         d = p ? td : d;
         idx = p ? ti : idx;
     }
+}
+// A newcomer that beats the K'-th entry lands at a uniformly distributed rank, so the chain is entered at the
+// 16-entry block that holds its position instead of at the head (2.5 of 4 blocks on average for K' = 64).
+template <int K>
+__device__ __forceinline__ void list_insert(float (&ld)[K], uint32_t (&li)[K], float d, uint32_t idx) {
+    static_assert(K % 16 == 0 && K >= 16 && K <= 64, "K' list is walked in blocks of 16");
+    if (K > 48 && !(d < ld[K - 49])) { list_insert_from<K, (K > 48 ? K - 48 : 0)>(ld, li, d, idx); return; }
+    if (K > 32 && !(d < ld[K - 33])) { list_insert_from<K, (K > 32 ? K - 32 : 0)>(ld, li, d, idx); return; }
+    if (K > 16 && !(d < ld[K - 17])) { list_insert_from<K, (K > 16 ? K - 16 : 0)>(ld, li, d, idx); return; }
+    list_insert_from<K, 0>(ld, li, d, idx);
 }
 
 struct TcSmem {
@@ -290,9 +300,8 @@ tnf_select_tc_kernel(const float *__restrict__ hi, const float *__restrict__ lo,
     if (warp == 1) tmem_dealloc(tmem);
 }
 
-template <int VARIANT>
+template <int VARIANT, int K>
 int32_t launch_tc(rg_handle *h, uint64_t q_begin, uint64_t q_count) {
-    constexpr int K = 64;
     const uint32_t D4 = h->d / 4;
     const size_t smem = (size_t)2 * D4 * SLICE_BYTES + (size_t)STAGES * STAGE_BYTES + sizeof(TcSmem);
     auto kern = tnf_select_tc_kernel<VARIANT, K>;
@@ -309,15 +318,20 @@ int32_t launch_tc(rg_handle *h, uint64_t q_begin, uint64_t q_count) {
 
 }  // namespace
 
-// The tensor-core kernel keeps its K' list in registers, so it serves K' = 64 (k <= 48, which covers the
+// The tensor-core kernel keeps its K' list in registers, so it serves K' = 48 / 64 (k <= 48, which covers the
 // reference's k = 30); K steps of 8 need d % 8 == 0 and the two query planes must fit beside the ring.
 bool rg_tnf_select_tc_supported(const rg_handle *h, uint32_t kprime) {
     const size_t smem = (size_t)2 * (h->d / 4) * SLICE_BYTES + (size_t)STAGES * STAGE_BYTES + sizeof(TcSmem);
-    return kprime == 64 && h->d % 8 == 0 && smem <= 227 * 1024;
+    return (kprime == 48 || kprime == 64) && h->d % 8 == 0 && smem <= 227 * 1024;
 }
 
-int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint64_t q_begin, uint64_t q_count) {
-    if (which == RG_GRAPH_TNF_EUCLID) return launch_tc<METRIC_EUCLID>(h, q_begin, q_count);
-    return h->variant == RG_VARIANT_FLIGHT ? launch_tc<RG_VARIANT_FLIGHT>(h, q_begin, q_count)
-                                           : launch_tc<RG_VARIANT_RUST>(h, q_begin, q_count);
+template <int K>
+static int32_t launch_tc_k(rg_handle *h, uint32_t which, uint64_t q_begin, uint64_t q_count) {
+    if (which == RG_GRAPH_TNF_EUCLID) return launch_tc<METRIC_EUCLID, K>(h, q_begin, q_count);
+    return h->variant == RG_VARIANT_FLIGHT ? launch_tc<RG_VARIANT_FLIGHT, K>(h, q_begin, q_count)
+                                           : launch_tc<RG_VARIANT_RUST, K>(h, q_begin, q_count);
+}
+
+int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+    return kprime == 48 ? launch_tc_k<48>(h, which, q_begin, q_count) : launch_tc_k<64>(h, which, q_begin, q_count);
 }
