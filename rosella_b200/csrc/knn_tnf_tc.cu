@@ -105,29 +105,27 @@ __device__ __forceinline__ float tmem_ld1(uint32_t taddr) {
 // ---------------------------------------------------------------- per-thread sorted list in registers
 // ld ascending; a new entry goes AFTER equal ones (candidates arrive in increasing index order, so ties stay
 // ordered by index).  Fully unrolled compare-exchange chain: no dynamic register indexing.
-template <int K, int START>
-__device__ __forceinline__ void list_insert_from(float (&ld)[K], uint32_t (&li)[K], float d, uint32_t idx) {
-    bool p = false;
-#pragma unroll
-    for (int e = START; e < K; ++e) {
-        p = p || d < ld[e];                  // once displaced, everything behind moves down by one
-        const float td = ld[e];
-        const uint32_t ti = li[e];
-        ld[e] = p ? d : td;
-        li[e] = p ? idx : ti;
-        d = p ? td : d;
-        idx = p ? ti : idx;
-    }
-}
-// A newcomer that beats the K'-th entry lands at a uniformly distributed rank, so the chain is entered at the
-// 16-entry block that holds its position instead of at the head (2.5 of 4 blocks on average for K' = 64).
+// A newcomer that beats the K'-th entry lands at a uniformly distributed rank, so the 16-entry blocks ahead of its
+// position are skipped (2 of 3 blocks run on average for K' = 48); one copy of each block keeps the code small.
 template <int K>
 __device__ __forceinline__ void list_insert(float (&ld)[K], uint32_t (&li)[K], float d, uint32_t idx) {
-    static_assert(K % 16 == 0 && K >= 16 && K <= 64, "K' list is walked in blocks of 16");
-    if (K > 48 && !(d < ld[K - 49])) { list_insert_from<K, (K > 48 ? K - 48 : 0)>(ld, li, d, idx); return; }
-    if (K > 32 && !(d < ld[K - 33])) { list_insert_from<K, (K > 32 ? K - 32 : 0)>(ld, li, d, idx); return; }
-    if (K > 16 && !(d < ld[K - 17])) { list_insert_from<K, (K > 16 ? K - 16 : 0)>(ld, li, d, idx); return; }
-    list_insert_from<K, 0>(ld, li, d, idx);
+    static_assert(K % 16 == 0, "K' list is walked in blocks of 16");
+    bool p = false;
+#pragma unroll
+    for (int blk = 0; blk < K / 16; ++blk) {
+        if (blk == K / 16 - 1 || p || d < ld[blk * 16 + 15]) {
+#pragma unroll
+            for (int e = blk * 16; e < blk * 16 + 16; ++e) {
+                p = p || d < ld[e];          // once displaced, everything behind moves down by one
+                const float td = ld[e];
+                const uint32_t ti = li[e];
+                ld[e] = p ? d : td;
+                li[e] = p ? idx : ti;
+                d = p ? td : d;
+                idx = p ? ti : idx;
+            }
+        }
+    }
 }
 
 struct TcSmem {
@@ -135,6 +133,7 @@ struct TcSmem {
     uint64_t tfull[2], tempty[2];           // accumulators: MMA -> epilogue, epilogue -> MMA
     uint64_t qfull;                         // query planes landed
     uint32_t tmem_base;
+    float nbuf[2][TN], mbuf[2][TN];         // norms / means of the reference rows of the panel in each accumulator
 };
 
 template <int VARIANT, int K>
@@ -221,6 +220,7 @@ tnf_select_tc_kernel(const float *__restrict__ hi, const float *__restrict__ lo,
         // ===================================================== epilogue: thread = query row
         const uint32_t quad = warp & 3;                      // the TMEM lane quadrant this warp may read
         const uint32_t row = quad * 32 + lane;
+        const uint32_t et = tid - 64;                        // 0..127 among the epilogue threads
         const uint32_t qrow = qpanel * TQ + row;
         const bool q_ok = qrow >= q_begin && qrow < q_begin + q_count && qrow < n;
         const float nq = norm[qrow], mq = VARIANT == METRIC_EUCLID ? mean[qrow] : 0.f;
@@ -229,58 +229,60 @@ tnf_select_tc_kernel(const float *__restrict__ hi, const float *__restrict__ lo,
         uint32_t li[K];
 #pragma unroll
         for (int e = 0; e < K; ++e) { ld[e] = INFINITY; li[e] = 0xffffffffu; }
-        float thr = INFINITY, coef = INFINITY;
+        // RUST / FLIGHT: d < thr  <=>  dot + coef (nq + nr) > 0 with coef = thr - 1/2 or (thr - 1)/2, tested as
+        // !(fma(coef, nr, dot) < c0), c0 = -coef nq; NaN (flagged rows, inf * 0) and equality (two constant rows)
+        // pass too and are settled by the exact form.  EUCLID: d^2 = nq + nr - 2 dot + dim (mu_q - mu_r)^2 < thr.
+        float thr = INFINITY, coef = INFINITY, c0 = -coef * nq;
+        float n_next = norm[et], m_next = VARIANT == METRIC_EUCLID ? mean[et] : 0.f;   // panel 0, this thread's column
         for (uint32_t p = 0; p < n_panels; ++p) {
             const uint32_t b = p & 1;
-            // norms (and means) of the panel's 128 reference rows: 4 per lane, handed round by shuffles
-            float nrv[4], mrv[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                nrv[k] = norm[p * TN + k * 32 + lane];
-                mrv[k] = VARIANT == METRIC_EUCLID ? mean[p * TN + k * 32 + lane] : 0.f;
+            // norms (and means) of the panel's 128 reference rows go through shared memory (broadcast reads);
+            // buffer b was last read two panels ago and every epilogue thread has passed a barrier since
+            sm.nbuf[b][et] = n_next;
+            if (VARIANT == METRIC_EUCLID) sm.mbuf[b][et] = m_next;
+            if (p + 1 < n_panels) {
+                n_next = norm[(p + 1) * TN + et];
+                if (VARIANT == METRIC_EUCLID) m_next = mean[(p + 1) * TN + et];
             }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
             mbar_wait(&sm.tfull[b], (p >> 1) & 1);
             tc_fence_after();
-#pragma unroll
+#pragma unroll 1
             for (int cc = 0; cc < 4; ++cc) {
                 const uint32_t taddr = tmem + ((quad * 32u) << 16) + b * TN + cc * 32;
+                const float *nb = &sm.nbuf[b][cc * 32], *mb = &sm.mbuf[b][cc * 32];
                 float acc[32];
                 tmem_ld32(taddr, acc);
-                // Pass 1, branch-free: one bit per column that may beat this row's K'-th distance.
-                //   RUST / FLIGHT: d < thr  <=>  dot + coef * den > 0 with coef = thr - 1/2 or (thr - 1)/2; NaN
-                //   (flagged rows, inf * 0) and 0 (two constant rows) also pass and are settled by the exact form.
-                //   EUCLID: d^2 = den - 2 dot + dim (mu_q - mu_r)^2 < thr.
+                // pass 1, branch-free: one bit per column that may beat this row's K'-th distance
                 uint32_t mask = 0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const float den = nq + __shfl_sync(0xffffffffu, nrv[cc], j);
                     bool pass;
                     if (VARIANT == METRIC_EUCLID) {
-                        const float dm = mq - __shfl_sync(0xffffffffu, mrv[cc], j);
-                        pass = !(thr - (fmaf(-2.0f, acc[j], den) + dim * dm * dm) <= 0.f);
+                        const float dm = mq - mb[j];
+                        pass = !(thr - (fmaf(-2.0f, acc[j], nq + nb[j]) + dim * dm * dm) <= 0.f);
                     } else {
-                        pass = !(fmaf(coef, den, acc[j]) < 0.f);
+                        pass = !(fmaf(coef, nb[j], acc[j]) < c0);
                     }
                     if (pass) mask |= 1u << j;
                 }
-                // Pass 2, rare: the warp walks the union of its lanes' columns; the column's accumulator is read
-                // back from TMEM (no dynamic register indexing) and the lanes that flagged it insert.
+                // pass 2, rare: the warp walks the union of its lanes' columns; the column's accumulator is read
+                // back from TMEM (no dynamic register indexing) and the lanes that flagged it insert
                 uint32_t wm = __reduce_or_sync(0xffffffffu, mask);
                 while (wm) {
                     const int j = __ffs(wm) - 1;
                     wm &= wm - 1;
                     const float dot = tmem_ld1(taddr + j);
-                    const float nr = __shfl_sync(0xffffffffu, nrv[cc], j);
-                    const float mr = VARIANT == METRIC_EUCLID ? __shfl_sync(0xffffffffu, mrv[cc], j) : 0.f;
                     if ((mask >> j) & 1u) {
                         const uint32_t ridx = p * TN + cc * 32 + j;
-                        const float dm = mq - mr;
-                        float d = tnf_finish<VARIANT>(dot, nq, nr, dim * dm * dm);
+                        const float dm = VARIANT == METRIC_EUCLID ? mq - mb[j] : 0.f;
+                        float d = tnf_finish<VARIANT>(dot, nq, nb[j], dim * dm * dm);
                         if (ridx >= n || ridx == qrow || !q_ok) d = INFINITY;
                         if (d < thr) {
                             list_insert<K>(ld, li, d, ridx);
                             thr = ld[K - 1];
                             coef = VARIANT == RG_VARIANT_RUST ? thr - 0.5f : 0.5f * (thr - 1.0f);
+                            c0 = -coef * nq;
                         }
                     }
                 }
