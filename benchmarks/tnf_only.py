@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """TNF counting leg alone (BASELINE.json configs[3]): python benchmarks/tnf_only.py [--gbp 10] [--steps 5]
-RG_TNF_IMPL=1 selects the first-generation kernels for an A/B line."""
+The first-generation (shared-memory atomics) numbers are kept in profiles/r1d_tnf_4gbp_v1.json."""
 import argparse
 import json
 import os
@@ -21,5 +21,5 @@ hbm = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEA
 with gpu.Context(0) as ctx:
     t = tnf_arm.run(ctx, int(a.gbp * 1e9), a.steps, a.warmup, hbm, min(32, os.cpu_count() or 8))
     t.pop("sample")
-    t["impl"] = "v1 (shared atomics)" if os.environ.get("RG_TNF_IMPL") == "1" else "v2 (byte counters)"
+    t["impl"] = "thread-private byte counters (tnf_count2.cu)"
     print(json.dumps(t))

@@ -1,15 +1,35 @@
-// knn_depth2.cu — K2a, second generation: the coverage ("depth") select kernel with the FP32 work
-// of TWO query rows packed into f32x2 instructions (pk.cuh).  Same metric, mapping, shared-memory
-// ring and top-K' lists as knn_depth.cu (read its header first); what changes is the issue cost:
-//   measured on B200 (profiles/r1_microbench_issue_model.json): FFMA 1 cycle/warp, FFMA2 2 cycles
-//   for twice the work, every ALU-pipe op (FSEL, FSETP, FMNMX, LOP3) 2 cycles, MUFU 8 cycles of the
-//   XU pipe.  v1 spent 57 FMA + 19 ALU + 7 MUFU instructions per (pair, sample); here
-//     - the FMA-pipe work is issued as f32x2 (half the issue slots),
-//     - the erf polynomial needs no clamp: degree 7 with a positive leading coefficient, so
-//       t*g(t) grows monotonically past the fitted range and 2^-(t g) underflows to 0 (4 FMNMX gone),
-//     - the equal-variance branch is blended arithmetically (r = 0 and a signed half-difference
-//       he select it) instead of four FSELs, sqrt takes |q| as a source modifier, and the
-//       accumulators are updated by predicated FADDs instead of FSEL + FADD.
+// knn_depth2.cu — K2a: fused coverage ("depth") distance + per-row top-K' selection.
+//
+// Metric: MetabatDistance::distance, src/coverage/coverage_calculator.rs:588-666 (variant RUST) or
+// metabat_distance_nn, flight/flight/metrics.py:445-538 (variant FLIGHT), evaluated in FP32 on the CUDA cores with
+// the per-contig terms (ln var', 1/(sd*sqrt2)) precomputed by knn_transform.cu.  This kernel only SELECTS K' >= k
+// candidates per query row; knn_rescore.cu re-evaluates them with the reference's f64 arithmetic, so the FP32 error
+// here can only perturb membership at the K' boundary, never a reported distance.
+//
+// Mapping: CTA = 8 warps = 32 query rows; a warp owns 4 query rows as two f32x2-packed pairs (pk.cuh) and its 32
+// lanes hold 32 consecutive reference rows.  Reference tiles (32 rows x SC samples x float4) stream through a
+// 2-stage shared-memory ring of 1-D TMA bulk copies (cp.async.bulk + mbarrier).  Each query's sorted K' list lives
+// in shared memory and is owned by its warp (rg_internal.cuh: topk_offer / topk_insert).
+//
+// Algebra (derivation in DESIGN.md §4.2).  With D = ma - mb, n = vb - va, r = 1/n,
+//   tmp = sqrt(va vb (D^2 + n (ln vb - ln va))), the two intersection points k+- of the normal pdfs give
+//   (k+- - ma)/(sa sqrt2) = (+-tmp - va D) r ia,   (k+- - mb)/(sb sqrt2) = (+-tmp - vb D) r ib
+//   and d = 1/2 |erf(xa+) - erf(xa-) - erf(xb+) + erf(xb-)|: no sorting of k1, k2 and no choice of the narrower
+//   distribution is needed because |.| absorbs both sign flips (coverage_calculator.rs:630-651).
+//   Equal-variance branch (:620-623): d = 1/2 (+-)(erf(D ia / 2) + erf(D ib / 2)), sign from :638 (RUST keeps the
+//   sign, so ln of a negative d turns the whole pair into NaN -> 1.0, :659-661).
+//
+// Issue cost, measured on B200 (profiles/r1_microbench_issue_model.json): FFMA 1 cycle/warp, FFMA2 2 pipe cycles
+// for twice the work but one dispatch slot, every ALU-pipe op (FSEL, FSETP, FMNMX, LOP3) 2 cycles, MUFU 8 cycles of
+// the XU pipe.  Hence
+//     - the FMA-pipe work of two query rows is issued as f32x2,
+//     - the erf polynomial needs no clamp: a positive leading coefficient makes t*g(t) grow monotonically past the
+//       fitted range, so 2^-(t g) underflows to 0,
+//     - the equal-variance branch is blended arithmetically (r = 0 and a signed half-difference he select it)
+//       instead of four FSELs, sqrt takes |q| as a source modifier, and the accumulators are updated by predicated
+//       FADDs instead of FSEL + FADD.
+// Per (pair, sample): 7 MUFU (sqrt, rcp, 4 x ex2, lg2) = 56 XU cycles, ~49 FMA-pipe cycles, ~53 dispatch cycles; ncu
+// (profiles/r1c_ncu_full_summary.json) shows the XU pipe at 74 % and the FMA pipe at 66 % of peak.
 #include <algorithm>
 
 #include "pk.cuh"
@@ -256,7 +276,8 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 
 }  // namespace
 
-int32_t rg_launch_depth_select_v2(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
+// cand_d / cand_i must hold q_count * kprime entries
+int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);
 }

@@ -5,22 +5,12 @@
 #include "rg_internal.cuh"
 #include "tnf_tables.h"
 
-int32_t rg_tnf_launch_packed(rg_handle *h);
-int32_t rg_tnf_launch_ascii(rg_handle *h);
 int32_t rg_tnf_launch_freq(rg_handle *h);
-uint32_t rg_tnf_chunk_words();
-uint32_t rg_tnf_chunk_bytes();
-// second generation (tnf_count2.cu): thread-private byte counters; the product path
+// counting kernels (tnf_count2.cu): thread-private byte counters
 int32_t rg_tnf_launch_packed2(rg_handle *h);
 int32_t rg_tnf_launch_ascii2(rg_handle *h);
 uint32_t rg_tnf2_chunk_units();
 uint32_t rg_tnf2_seg_bytes();
-
-// RG_TNF_IMPL=1 selects the first-generation (shared-memory atomics) kernels for A/B measurements
-static bool use_v1() {
-    static const bool v1 = [] { const char *e = getenv("RG_TNF_IMPL"); return e && e[0] == '1'; }();
-    return v1;
-}
 
 static int32_t ensure_tables(rg_handle *h) {
     if (h->tnf_tables.p) return RG_OK;
@@ -79,7 +69,7 @@ int32_t rg_tnf_load_packed(rg_handle *h, const uint64_t *codes, const uint32_t *
     RG_CUDA(h, cudaMemcpyAsync(h->valid.p, valid, words * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaMemcpyAsync(h->woff.p, word_offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
-    RG_TRY(upload_chunks(h, word_offsets, n, use_v1() ? rg_tnf_chunk_words() : rg_tnf2_chunk_units()));
+    RG_TRY(upload_chunks(h, word_offsets, n, rg_tnf2_chunk_units()));
     h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.h2d_bytes += words * 12 + (n + 1) * 16;
     h->tnf_n = n; h->tnf_words = words; h->tnf_bytes = 0; h->tnf_mode = 1;
@@ -103,8 +93,7 @@ int32_t rg_tnf_load_ascii(rg_handle *h, const uint8_t *seq, const uint64_t *offs
         RG_CUDA(h, cudaMemcpyAsync((uint8_t *)h->ascii.p + lo, seq + lo, hi - lo, cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaMemcpyAsync(h->aoff.p, offsets, (n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
-    if (use_v1()) RG_TRY(upload_chunks(h, offsets, n, rg_tnf_chunk_bytes()));
-    else RG_TRY(upload_chunks(h, offsets, n, rg_tnf2_chunk_units(), rg_tnf2_seg_bytes()));
+    RG_TRY(upload_chunks(h, offsets, n, rg_tnf2_chunk_units(), rg_tnf2_seg_bytes()));
     h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.h2d_bytes += (hi - lo) + (n + 1) * 16;
     h->tnf_n = n; h->tnf_words = 0; h->tnf_bytes = hi - lo; h->tnf_mode = 2;
@@ -117,8 +106,7 @@ int32_t rg_tnf_count_resident(rg_handle *h) {
     RG_CUDA(h, cudaSetDevice(h->device));
     RG_CUDA(h, cudaMemsetAsync(h->counts.p, 0, h->tnf_n * RG_NBINS * sizeof(uint32_t), h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[6], h->stream));
-    if (use_v1()) RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed(h) : rg_tnf_launch_ascii(h));
-    else RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed2(h) : rg_tnf_launch_ascii2(h));
+    RG_TRY(h->tnf_mode == 1 ? rg_tnf_launch_packed2(h) : rg_tnf_launch_ascii2(h));
     RG_CUDA(h, cudaEventRecord(h->ev[7], h->stream));
     RG_TRY(rg_tnf_launch_freq(h));
     h->tm.tnf_count_ms = -1.0;   // resolved lazily by rg_get_timings

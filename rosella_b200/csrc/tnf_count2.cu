@@ -1,9 +1,10 @@
-// tnf_count2.cu — K1, second generation: tetranucleotide counting with thread-private byte counters.
+// tnf_count2.cu — K1: tetranucleotide counting with thread-private byte counters.
 //
-// Same result as tnf_count.cu (KmerCounter::run, src/kmers/kmer_counting.rs:64-109: per record the
-// counts of the 136 canonical 4-mers over every window of 4 consecutive A/C/G/T bases); what changes
-// is how a window reaches its bin.  v1 paid a shared-memory atomic plus a LUT load per base and was
-// bound by the ALU/LSU pipes at 5 % of the HBM roofline (profiles/r1c_ncu_full_summary.json).  Here
+// Replaces the per-record loop of KmerCounter::run (src/kmers/kmer_counting.rs:64-109): for every window of 4
+// consecutive A/C/G/T bases of the normalised record, increment the bin of the lexicographically smaller of
+// (4-mer, reverse complement) (:82-101).  The first generation of this kernel paid a shared-memory atomic plus a LUT
+// load per base and was bound by the ALU/LSU pipes at 5 % of the HBM roofline (profiles/r1c_ncu_full_summary.json,
+// profiles/r1d_tnf_4gbp_v1.json).  Here
 //   * every thread owns one BYTE counter per raw 8-bit window code: counter (code, warp, lane) is byte
 //     (warp & 3) of the 32-bit word [code][lane] of a 32 KB plane shared by the 4 warps of a CTA, so a
 //     warp's 32 lanes always touch 32 different banks whatever their codes are (no conflicts), no two
