@@ -212,3 +212,39 @@ def test_graph_ops(ctx):
     for keep_n in (0, 5, 12):
         assert np.array_equal(ctx.graph_mutual(di, keep_n), oracle.mutual_knn(di, keep_n))
         assert np.array_equal(ctx.graph_intersect(di, ti, keep_n), oracle.intersect(di, ti, keep_n))
+
+
+def test_config1_full_build_100k(ctx):
+    """BASELINE.json configs[1]: 100k contigs x (136 TNF + 10 samples), k = 30, the whole graph on one B200 through
+    rg_knn_build; three blocks of rows are checked against the exhaustive f64 oracle, all rows against the
+    size-independent properties of a kNN list."""
+    n, s, k = 100_000, 10, 30
+    tnf, cov, _ = synth.knn_tables(n, s)
+    (ti, td), (di, dd) = ctx.knn_build(tnf, cov, k)
+    for idx, dist in ((ti, td), (di, dd)):
+        assert idx.shape == (n, k) and (idx != PAD).all() and (idx < n).all()
+        assert (idx != np.arange(n, dtype=np.uint32)[:, None]).all()             # self excluded
+        assert (np.diff(dist, axis=1) >= 0).all()                                  # ascending
+        srt = np.sort(idx, axis=1)
+        assert (srt[:, 1:] != srt[:, :-1]).all()                                   # no duplicates
+    for qb in (0, 50_016, n - 64):
+        r1, _ = check_against_oracle(tnf, oracle.TNF, oracle.RUST, k, ti[qb:qb + 64], td[qb:qb + 64], q_begin=qb)
+        r2, _ = check_against_oracle(cov, oracle.DEPTH, oracle.RUST, k, di[qb:qb + 64], dd[qb:qb + 64], q_begin=qb)
+        assert r1 == 1.0 and r2 == 1.0
+
+
+def test_config2_query_batch_1m(ctx):
+    """BASELINE.json configs[2] at full reference size: 1M contigs x (136 TNF + 50 samples), k = 30.  A batch of query
+    rows is searched against all 1M references (what one bench step does); 32 of them are checked against the
+    exhaustive f64 oracle, and a shifted batch must reproduce the overlapping rows bit for bit."""
+    n, s, k = 1_000_000, 50, 30
+    tnf, cov, _ = synth.knn_tables(n, s)
+    ctx.knn_load(tnf, cov, gpu.VARIANT_RUST)
+    qb = 700_000
+    for which, data, ow in ((gpu.GRAPH_DEPTH, cov, oracle.DEPTH), (gpu.GRAPH_TNF, tnf, oracle.TNF)):
+        idx, dist, nv = ctx.knn_search(which, k, qb, qb + 1024)
+        assert (nv == k).all() and (np.diff(dist, axis=1) >= 0).all()
+        recall, _ = check_against_oracle(data, ow, oracle.RUST, k, idx[:32], dist[:32], q_begin=qb)
+        assert recall == 1.0
+        idx2, dist2, _ = ctx.knn_search(which, k, qb + 96, qb + 96 + 512)          # another CTA / panel alignment
+        assert np.array_equal(idx2, idx[96:608]) and np.array_equal(dist2, dist[96:608])
