@@ -1,0 +1,245 @@
+// knn_depth_sym.cu — K2a': the coverage graph of ALL rows (rg_knn_build, rg_knn_search over [0, n)) with every
+// unordered pair evaluated once.
+//
+// The coverage metric (coverage_calculator.rs:588-666, metrics.py:445-538) is symmetric up to the sign rule of the
+// equal-variance branch (:638/:647, tracked apart — knn_depth_common.cuh SignTrack), and its evaluation is what the
+// build costs (knn_depth2.cu is bound by the XU / FMA pipes, not by memory).  The rows are cut into blocks of B; for
+// each block pair I <= J
+//   1. depth_tile_kernel evaluates the B x B distances of rows I against rows J (same CTA mapping, TMA ring and FP32
+//      arithmetic as knn_depth2.cu) and writes them twice: Dm[i][j] as row i sees the pair, Dt[j][i] as row j does;
+//   2. topk_reduce_kernel streams Dm into the K' lists of the rows of I, and (J > I) Dt into those of the rows of J.
+// The lists live in the candidate arrays [n][K'] that knn_rescore.cu reads, so the f64 re-evaluation is unchanged.
+// The reduction is bandwidth work (one coalesced pass over 2 B^2 floats per pair, ~4 % of the evaluation time) and
+// keeps the evaluation kernel free of cross-row traffic: an earlier attempt that pushed each distance into both rows'
+// lists from inside the evaluation kernel was slower than evaluating every pair twice.
+//
+// Order: candidates reach the list of a row in increasing reference index (blocks I' < I deliver their columns while
+// the outer loop is at I', then the row's own pass runs over J = I, I+1, ...), which is the arrival order topk_insert
+// needs for the (distance, index) tie rule.
+#include <cstdlib>
+
+#include "knn_depth_common.cuh"
+
+namespace {
+
+using namespace depthk;
+
+constexpr int QPW = 4;
+constexpr int WARPS = 8;
+constexpr int QB = QPW * WARPS;
+constexpr int PAIRS = QB / 2;
+
+// rows [q0base + 32 b, +32) against reference tiles [t_begin, t_begin + n_tiles_blk); Dm pitch_m floats per row
+// (>= 32 n_tiles_blk), Dt (may be null) pitch_t floats per row (>= 32 gridDim.x)
+template <int VARIANT>
+__global__ void __launch_bounds__(WARPS * 32, 2)
+depth_tile_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, uint32_t SC, uint32_t q0base,
+                  uint32_t t_begin, uint32_t n_tiles_blk, float *__restrict__ Dm, uint32_t pitch_m,
+                  float *__restrict__ Dt, uint32_t pitch_t) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t tile_f4 = S * RG_TILE, stage_f4 = SC * RG_TILE;
+    float4 *stage[2] = {reinterpret_cast<float4 *>(smem), reinterpret_cast<float4 *>(smem) + stage_f4};
+    float *qd = reinterpret_cast<float *>(stage[1] + stage_f4);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(qd + tile_f4 * 4);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t q0 = q0base + blockIdx.x * QB;
+    for (uint32_t i = tid; i < tile_f4; i += WARPS * 32) {
+        const uint32_t s = i / RG_TILE, r = i % RG_TILE;
+        const uint32_t row = min(q0 + r, n - 1);
+        const float4 v = cov_t[((uint64_t)(row / RG_TILE) * S + s) * RG_TILE + row % RG_TILE];
+        float *dst = qd + ((s * PAIRS + (r >> 1)) * 8) + (r & 1);
+        dst[0] = v.x; dst[2] = v.y; dst[4] = v.z; dst[6] = v.w;
+    }
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const uint32_t n_chunks = (S + SC - 1) / SC;
+    const uint32_t n_stages = n_tiles_blk * n_chunks;
+    auto issue = [&](uint32_t g) {
+        const uint32_t t = t_begin + g / n_chunks, c = g % n_chunks;
+        const uint32_t len = min(SC, S - c * SC);
+        const uint32_t bytes = len * RG_TILE * (uint32_t)sizeof(float4);
+        uint64_t *bar = &bars[g & 1];
+        mbar_expect_tx(bar, bytes);
+        tma_bulk_g2s(stage[g & 1], cov_t + ((uint64_t)t * S + (uint64_t)c * SC) * RG_TILE, bytes, bar);
+    };
+    if (tid == 0) issue(0);
+    const ulonglong2 *qp = reinterpret_cast<const ulonglong2 *>(qd) + warp * 4;
+    const uint32_t ql = blockIdx.x * QB + warp * QPW;      // first of this warp's 4 rows, local to the block
+
+    float acc[QPW], cnt[QPW];
+    SignTrack st[2];
+#pragma unroll
+    for (int u = 0; u < QPW; ++u) acc[u] = cnt[u] = 0.f;
+    st[0] = st[1] = SignTrack{0.f, 0.f, 0.f, 0.f};
+    uint32_t t = 0, c = 0;
+    for (uint32_t g = 0; g < n_stages; ++g) {
+        __syncthreads();
+        if (tid == 0 && g + 1 < n_stages) issue(g + 1);
+        mbar_wait(&bars[g & 1], (g >> 1) & 1);
+        const float4 *ref = stage[g & 1];
+        const uint32_t s0 = c * SC, len = min(SC, S - s0);
+        const ulonglong2 *qs = qp + (size_t)s0 * (PAIRS * 2);
+#pragma unroll 2
+        for (uint32_t s = 0; s < len; ++s) {
+            const float4 b = ref[s * RG_TILE + lane];
+#pragma unroll
+            for (int pr = 0; pr < 2; ++pr) {
+                const ulonglong2 xy = qs[s * (PAIRS * 2) + pr * 2], zw = qs[s * (PAIRS * 2) + pr * 2 + 1];
+                depth_sample2<VARIANT, true>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc[2 * pr], cnt[2 * pr],
+                                             acc[2 * pr + 1], cnt[2 * pr + 1], st[pr]);
+            }
+        }
+        if (++c == n_chunks) {
+            const uint32_t col = t * RG_TILE + lane;
+            const float mnf[QPW] = {st[0].mnf0, st[0].mnf1, st[1].mnf0, st[1].mnf1};
+            const float mnb[QPW] = {st[0].mnb0, st[0].mnb1, st[1].mnb0, st[1].mnb1};
+            float dk[QPW];
+#pragma unroll
+            for (int u = 0; u < QPW; ++u) {
+                const float dc = depth_finish<VARIANT>(acc[u], cnt[u]);
+                float df = dc;
+                dk[u] = dc;
+                if (VARIANT == RG_VARIANT_RUST) {
+                    if (mnf[u] < 0.f) df = 1.0f;          // ln of a negative value -> NaN -> 1.0 (:659-661)
+                    if (mnb[u] < 0.f) dk[u] = 1.0f;       // the same pair seen from the reference row
+                }
+                Dm[(size_t)(ql + u) * pitch_m + col] = df;
+                acc[u] = cnt[u] = 0.f;
+            }
+            if (Dt) *reinterpret_cast<float4 *>(Dt + (size_t)col * pitch_t + ql) = make_float4(dk[0], dk[1], dk[2], dk[3]);
+            st[0] = st[1] = SignTrack{0.f, 0.f, 0.f, 0.f};
+            c = 0;
+            ++t;
+        }
+    }
+}
+
+// One warp per list row: merge the row's pitch-padded line of M (columns = global rows col0, col0+1, ...) into its
+// sorted K' list in cand_d / cand_i [n][K].
+template <int K>
+__global__ void __launch_bounds__(WARPS * 32)
+topk_reduce_kernel(const float *__restrict__ M, uint32_t pitch, uint32_t n_cols, uint32_t row0, uint32_t n_rows,
+                   uint32_t col0, uint32_t n, float *__restrict__ cand_d, uint32_t *__restrict__ cand_i) {
+    __shared__ float s_d[WARPS][K];
+    __shared__ uint32_t s_i[WARPS][K];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t r = blockIdx.x * WARPS + warp;
+    if (r >= n_rows || row0 + r >= n) return;
+    const uint32_t grow = row0 + r;
+    float *ld = s_d[warp];
+    uint32_t *li = s_i[warp];
+    for (int e = lane; e < K; e += 32) {
+        ld[e] = cand_d[(uint64_t)grow * K + e];
+        li[e] = cand_i[(uint64_t)grow * K + e];
+    }
+    __syncwarp();
+    float thr = ld[K - 1];
+    const float *line = M + (size_t)r * pitch;
+    for (uint32_t c = 0; c < n_cols; c += 128) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t cc = c + j * 32 + lane;
+            v[j] = cc < n_cols ? __ldcs(line + cc) : INFINITY;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t gi = col0 + c + j * 32 + lane;
+            const float d = (gi >= n || gi == grow) ? INFINITY : v[j];
+            topk_offer<K>(ld, li, d, gi, thr, lane);
+        }
+    }
+    __syncwarp();
+    for (int e = lane; e < K; e += 32) {
+        cand_d[(uint64_t)grow * K + e] = ld[e];
+        cand_i[(uint64_t)grow * K + e] = li[e];
+    }
+}
+
+__global__ void list_init_kernel(float *cand_d, uint32_t *cand_i, uint64_t count) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < count; i += (uint64_t)gridDim.x * blockDim.x) {
+        cand_d[i] = INFINITY;
+        cand_i[i] = 0xffffffffu;
+    }
+}
+
+uint32_t block_rows(const rg_handle *h) {
+    // 18944 = 592 x 32: the evaluation grid of a full block is exactly two waves of 148 SMs x 2 CTAs
+    uint64_t b = 592ull * QB;
+    if (const char *e = getenv("RG_SYM_BLOCK")) {
+        const long v = atol(e);
+        if (v > 0) b = (uint64_t)v;
+    }
+    b = (b + QB - 1) / QB * QB;
+    return (uint32_t)std::min<uint64_t>(b, h->n_tiles * RG_TILE);
+}
+
+template <int VARIANT, int K>
+int32_t build(rg_handle *h) {
+    const uint32_t n = (uint32_t)h->n, S = h->s, B = block_rows(h);
+    const uint32_t nb = (n + B - 1) / B;
+    const size_t tile_bytes = (size_t)S * RG_TILE * sizeof(float4);
+    size_t smem = 0;
+    const uint32_t sc = pick_chunk(S, tile_bytes + 2 * sizeof(uint64_t), smem);
+    if (sc == 0)
+        return rg_fail(h, RG_ERR_INVALID, "depth build: %u samples need %zu bytes of shared memory for the query rows alone (> 227 KB)",
+                       S, tile_bytes);
+    RG_TRY(rg_reserve(h, h->sym_d, (size_t)B * B * sizeof(float)));
+    RG_TRY(rg_reserve(h, h->sym_t, (size_t)B * B * sizeof(float)));
+    auto kern = depth_tile_kernel<VARIANT>;
+    RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    float *cd = (float *)h->cand_d.p;
+    uint32_t *ci = (uint32_t *)h->cand_i.p;
+    float *Dm = (float *)h->sym_d.p, *Dt = (float *)h->sym_t.p;
+    list_init_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(cd, ci, (uint64_t)n * K);
+    h->tm.kernel_launches += 1;
+    for (uint32_t I = 0; I < nb; ++I) {
+        const uint32_t i0 = I * B, ni = std::min(B, n - i0), ni_pad = (ni + QB - 1) / QB * QB;
+        for (uint32_t J = I; J < nb; ++J) {
+            const uint32_t j0 = J * B, nj = std::min(B, n - j0), nj_pad = (nj + RG_TILE - 1) / RG_TILE * RG_TILE;
+            const bool off = J > I;
+            kern<<<ni_pad / QB, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, n, S, sc, i0, j0 / RG_TILE,
+                                                               nj_pad / RG_TILE, Dm, nj_pad, off ? Dt : nullptr, ni_pad);
+            topk_reduce_kernel<K><<<(ni + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dm, nj_pad, nj_pad, i0, ni, j0,
+                                                                                         n, cd, ci);
+            h->tm.kernel_launches += 2;
+            if (off) {
+                topk_reduce_kernel<K><<<(nj + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dt, ni_pad, ni_pad, j0, nj,
+                                                                                             i0, n, cd, ci);
+                h->tm.kernel_launches += 1;
+            }
+        }
+        RG_CUDA(h, cudaGetLastError());
+    }
+    return RG_OK;
+}
+
+template <int VARIANT>
+int32_t build_k(rg_handle *h, uint32_t kprime) {
+    switch (kprime) {
+        case 64: return build<VARIANT, 64>(h);
+        case 128: return build<VARIANT, 128>(h);
+        case 256: return build<VARIANT, 256>(h);
+    }
+    return rg_fail(h, RG_ERR_INVALID, "depth build: unsupported K'=%u", kprime);
+}
+
+}  // namespace
+
+// Whole-graph builds take the symmetric path once there is more than one block of rows (below that it evaluates the
+// same square as the batch kernel); RG_DEPTH_BUILD=batch keeps the batch kernel, RG_SYM_BLOCK sets the block rows.
+bool rg_depth_build_sym_wanted(const rg_handle *h) {
+    if (const char *e = getenv("RG_DEPTH_BUILD"))
+        if (e[0] == 'b') return false;
+    return h->n > block_rows(h);
+}
+
+// cand_d / cand_i must hold n * kprime entries
+int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime) {
+    return h->variant == RG_VARIANT_FLIGHT ? build_k<RG_VARIANT_FLIGHT>(h, kprime) : build_k<RG_VARIANT_RUST>(h, kprime);
+}

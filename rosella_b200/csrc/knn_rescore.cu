@@ -193,6 +193,8 @@ int32_t launch_rescore(rg_handle *h, const double *data, uint32_t width, uint32_
 }  // namespace
 
 int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
+int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime);
+bool rg_depth_build_sym_wanted(const rg_handle *h);
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 uint32_t rg_tnf_kprime(const rg_handle *h, uint32_t k, uint32_t general);
 
@@ -224,7 +226,8 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
     RG_TRY(rg_reserve(h, h->cand_d, q_count * kprime * sizeof(float)));
     RG_TRY(rg_reserve(h, h->cand_i, q_count * kprime * sizeof(uint32_t)));
     RG_CUDA(h, cudaEventRecord(h->ev[3], h->stream));
-    if (which == RG_GRAPH_DEPTH) RG_TRY(rg_launch_depth_select(h, kprime, q_begin, q_count));
+    if (which == RG_GRAPH_DEPTH && q_count == h->n && rg_depth_build_sym_wanted(h)) RG_TRY(rg_launch_depth_build_sym(h, kprime));
+    else if (which == RG_GRAPH_DEPTH) RG_TRY(rg_launch_depth_select(h, kprime, q_begin, q_count));
     else RG_TRY(rg_launch_tnf_select(h, which, kprime, q_begin, q_count));
     RG_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
     const bool fl = h->variant == RG_VARIANT_FLIGHT;

@@ -83,7 +83,7 @@ void rg_destroy(rg_handle *h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf *bufs[] = {&h->tnf64, &h->cov64, &h->tnf_t, &h->tnf_norm, &h->tnf_mean, &h->tnf_hi, &h->tnf_lo, &h->cov_t, &h->err_flag,
-                      &h->cand_d, &h->cand_i, &h->out_i, &h->out_d, &h->out_nv, &h->codes, &h->valid,
+                      &h->cand_d, &h->cand_i, &h->sym_d, &h->sym_t, &h->out_i, &h->out_d, &h->out_nv, &h->codes, &h->valid,
                       &h->woff, &h->ascii, &h->aoff, &h->counts, &h->nkmers, &h->freqs, &h->tnf_tables,
                       &h->chunk_start};
     for (DevBuf *b : bufs) rg_release(*b);

@@ -40,6 +40,7 @@ struct rg_handle {
     DevBuf cov_t;             // float4 (mean, var, ln var, +-1/(sd*sqrt2)) tile-major [tile][s][32]
     DevBuf err_flag;          // u32 device error word (non-finite coverage, ...)
     DevBuf cand_d, cand_i;    // select-phase candidates [rows][kprime]
+    DevBuf sym_d, sym_t;      // symmetric depth build: one block pair of distances and its transpose (knn_depth_sym.cu)
     DevBuf out_i, out_d, out_nv; // device staging of final lists for host-output calls
 
     // ---- TNF counting state

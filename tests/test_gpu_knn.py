@@ -82,6 +82,33 @@ def test_knn_synthetic_3000(ctx, variant):
     assert e1 > 0.99 and e2 > 0.98
 
 
+@pytest.mark.parametrize("variant", [gpu.VARIANT_RUST, gpu.VARIANT_FLIGHT])
+@pytest.mark.parametrize("block", [256, 992])
+def test_depth_symmetric_build(ctx, variant, block, monkeypatch):
+    """Whole-graph coverage builds evaluate each unordered pair once (knn_depth_sym.cu): the lists must equal the batch
+    kernel's bit for bit and pass the oracle checks, including rows in different blocks that share their variances
+    (the equal-variance branch whose sign depends on which row is the query, coverage_calculator.rs:638-647)."""
+    tnf, cov, _ = synth.knn_tables(3000, 6, seed=21, flight=variant == gpu.VARIANT_FLIGHT)
+    cov[2500, 1::2] = cov[100, 1::2]            # equal variances across blocks, different means
+    cov[2501, 1::2] = cov[100, 1::2]
+    cov[101] = cov[2600]                        # duplicate rows across blocks
+    cov[7] = 0.0
+    cov[2999, 1::2] = 0.0
+    ctx.knn_load(None, cov, variant)
+    monkeypatch.setenv("RG_DEPTH_BUILD", "batch")
+    bi, bd, bnv = ctx.knn_search(gpu.GRAPH_DEPTH, 30)
+    monkeypatch.delenv("RG_DEPTH_BUILD")
+    monkeypatch.setenv("RG_SYM_BLOCK", str(block))
+    launches0 = ctx.timings()["kernel_launches"]
+    si, sd, snv = ctx.knn_search(gpu.GRAPH_DEPTH, 30)
+    nb = -(-3000 // block)
+    assert ctx.timings()["kernel_launches"] - launches0 >= nb * (nb + 1) // 2 * 2     # the block-pair path did run
+    assert np.array_equal(si, bi) and np.array_equal(sd, bd) and np.array_equal(snv, bnv)
+    sel = np.r_[90:110, 2490:2510, 2990:3000]
+    for r0 in (90, 2490, 2990):
+        check_against_oracle(cov, oracle.DEPTH, variant, 30, si[r0:r0 + 10], sd[r0:r0 + 10], q_begin=r0, min_recall=0.995)
+
+
 def test_knn_sharded_query_ranges(ctx):
     """Rank shards [q_begin, q_end) that are not tile aligned concatenate to the full result."""
     tnf, cov, _ = synth.knn_tables(1500, 5, seed=11)
