@@ -5,9 +5,10 @@
 // equal-variance branch (:638/:647, tracked apart — knn_depth_common.cuh SignTrack), and its evaluation is what the
 // build costs (knn_depth2.cu is bound by the XU / FMA pipes, not by memory).  The rows are cut into blocks of B; for
 // each block pair I <= J
-//   1. depth_tile_kernel evaluates the B x B distances of rows I against rows J (same CTA mapping, TMA ring and FP32
+//   1. depth_tile_kernel evaluates the distances of rows I against rows J (same CTA mapping, TMA ring and FP32
 //      arithmetic as knn_depth2.cu) and writes them twice: Dm[i][j] as row i sees the pair, Dt[j][i] as row j does;
 //   2. topk_reduce_kernel streams Dm into the K' lists of the rows of I, and (J > I) Dt into those of the rows of J.
+// (Several column blocks J are evaluated per launch; see build().)
 // The lists live in the candidate arrays [n][K'] that knn_rescore.cu reads, so the f64 re-evaluation is unchanged.
 // The reduction is bandwidth work (one coalesced pass over 2 B^2 floats per pair, ~4 % of the evaluation time) and
 // keeps the evaluation kernel free of cross-row traffic: an earlier attempt that pushed each distance into both rows'
@@ -168,29 +169,38 @@ __global__ void list_init_kernel(float *cand_d, uint32_t *cand_i, uint64_t count
     }
 }
 
-uint32_t block_rows(const rg_handle *h) {
-    // 18944 = 592 x 32: the evaluation grid of a full block is exactly two waves of 148 SMs x 2 CTAs
-    uint64_t b = 592ull * QB;
-    if (const char *e = getenv("RG_SYM_BLOCK")) {
+static uint64_t env_rows(const char *name, uint64_t dflt) {
+    if (const char *e = getenv(name)) {
         const long v = atol(e);
-        if (v > 0) b = (uint64_t)v;
+        if (v > 0) dflt = (uint64_t)v;
     }
-    b = (b + QB - 1) / QB * QB;
-    return (uint32_t)std::min<uint64_t>(b, h->n_tiles * RG_TILE);
+    return (dflt + QB - 1) / QB * QB;
 }
 
+// rows per block: 9472 = 296 x 32, one full wave of 148 SMs x 2 CTAs per evaluation launch
+uint32_t block_rows(const rg_handle *h) {
+    return (uint32_t)std::min<uint64_t>(env_rows("RG_SYM_BLOCK", 296ull * QB), h->n_tiles * RG_TILE);
+}
+
+// columns per evaluation launch (the width of the distance buffers): 4 blocks
+uint32_t chunk_cols(const rg_handle *h, uint32_t B) {
+    return (uint32_t)std::min<uint64_t>(env_rows("RG_SYM_CHUNK", 4ull * B), h->n_tiles * RG_TILE);
+}
+
+// Block I = rows [i0, i0 + ni) is evaluated against the columns [i0, n) in chunks: its own square in full (both
+// orders of a pair inside the block are computed, B / 2N of the work) and everything to the right once.  Dm feeds the
+// lists of the block's rows, Dt those of the columns right of the block.
 template <int VARIANT, int K>
 int32_t build(rg_handle *h) {
-    const uint32_t n = (uint32_t)h->n, S = h->s, B = block_rows(h);
-    const uint32_t nb = (n + B - 1) / B;
+    const uint32_t n = (uint32_t)h->n, S = h->s, B = block_rows(h), C = chunk_cols(h, B);
     const size_t tile_bytes = (size_t)S * RG_TILE * sizeof(float4);
     size_t smem = 0;
     const uint32_t sc = pick_chunk(S, tile_bytes + 2 * sizeof(uint64_t), smem);
     if (sc == 0)
         return rg_fail(h, RG_ERR_INVALID, "depth build: %u samples need %zu bytes of shared memory for the query rows alone (> 227 KB)",
                        S, tile_bytes);
-    RG_TRY(rg_reserve(h, h->sym_d, (size_t)B * B * sizeof(float)));
-    RG_TRY(rg_reserve(h, h->sym_t, (size_t)B * B * sizeof(float)));
+    RG_TRY(rg_reserve(h, h->sym_d, (size_t)B * C * sizeof(float)));
+    RG_TRY(rg_reserve(h, h->sym_t, (size_t)B * C * sizeof(float)));
     auto kern = depth_tile_kernel<VARIANT>;
     RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     float *cd = (float *)h->cand_d.p;
@@ -198,19 +208,19 @@ int32_t build(rg_handle *h) {
     float *Dm = (float *)h->sym_d.p, *Dt = (float *)h->sym_t.p;
     list_init_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(cd, ci, (uint64_t)n * K);
     h->tm.kernel_launches += 1;
-    for (uint32_t I = 0; I < nb; ++I) {
-        const uint32_t i0 = I * B, ni = std::min(B, n - i0), ni_pad = (ni + QB - 1) / QB * QB;
-        for (uint32_t J = I; J < nb; ++J) {
-            const uint32_t j0 = J * B, nj = std::min(B, n - j0), nj_pad = (nj + RG_TILE - 1) / RG_TILE * RG_TILE;
-            const bool off = J > I;
-            kern<<<ni_pad / QB, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, n, S, sc, i0, j0 / RG_TILE,
-                                                               nj_pad / RG_TILE, Dm, nj_pad, off ? Dt : nullptr, ni_pad);
-            topk_reduce_kernel<K><<<(ni + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dm, nj_pad, nj_pad, i0, ni, j0,
+    for (uint32_t i0 = 0; i0 < n; i0 += B) {
+        const uint32_t ni = std::min(B, n - i0), ni_pad = (ni + QB - 1) / QB * QB, i1 = i0 + ni;
+        for (uint32_t c0 = i0; c0 < n; c0 += C) {
+            const uint32_t nc = std::min(C, n - c0), nc_pad = (nc + RG_TILE - 1) / RG_TILE * RG_TILE, c1 = c0 + nc;
+            const uint32_t jb = std::max(c0, i1);          // first column right of the block
+            kern<<<ni_pad / QB, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, n, S, sc, i0, c0 / RG_TILE,
+                                                               nc_pad / RG_TILE, Dm, nc_pad, jb < c1 ? Dt : nullptr, ni_pad);
+            topk_reduce_kernel<K><<<(ni + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dm, nc_pad, nc_pad, i0, ni, c0,
                                                                                          n, cd, ci);
             h->tm.kernel_launches += 2;
-            if (off) {
-                topk_reduce_kernel<K><<<(nj + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dt, ni_pad, ni_pad, j0, nj,
-                                                                                             i0, n, cd, ci);
+            if (jb < c1) {
+                topk_reduce_kernel<K><<<(c1 - jb + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(
+                    Dt + (size_t)(jb - c0) * ni_pad, ni_pad, ni_pad, jb, c1 - jb, i0, n, cd, ci);
                 h->tm.kernel_launches += 1;
             }
         }
@@ -232,7 +242,8 @@ int32_t build_k(rg_handle *h, uint32_t kprime) {
 }  // namespace
 
 // Whole-graph builds take the symmetric path once there is more than one block of rows (below that it evaluates the
-// same square as the batch kernel); RG_DEPTH_BUILD=batch keeps the batch kernel, RG_SYM_BLOCK sets the block rows.
+// same square as the batch kernel); RG_DEPTH_BUILD=batch keeps the batch kernel, RG_SYM_BLOCK / RG_SYM_CHUNK set the
+// block rows and the columns per launch.
 bool rg_depth_build_sym_wanted(const rg_handle *h) {
     if (const char *e = getenv("RG_DEPTH_BUILD"))
         if (e[0] == 'b') return false;
