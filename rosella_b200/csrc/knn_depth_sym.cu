@@ -29,6 +29,7 @@ constexpr int QPW = 4;
 constexpr int WARPS = 8;
 constexpr int QB = QPW * WARPS;
 constexpr int PAIRS = QB / 2;
+constexpr int RWARPS = 4;      // reducer CTA: 128 threads x 32 registers fit beside two evaluation CTAs on an SM
 
 // rows [q0base + 32 b, +32) against reference tiles [t_begin, t_begin + n_tiles_blk); Dm pitch_m floats per row
 // (>= 32 n_tiles_blk), Dt (may be null) pitch_t floats per row (>= 32 gridDim.x)
@@ -123,13 +124,13 @@ depth_tile_kernel(const float4 *__restrict__ cov_t, uint32_t n, uint32_t S, uint
 // One warp per list row: merge the row's pitch-padded line of M (columns = global rows col0, col0+1, ...) into its
 // sorted K' list in cand_d / cand_i [n][K].
 template <int K>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(RWARPS * 32)
 topk_reduce_kernel(const float *__restrict__ M, uint32_t pitch, uint32_t n_cols, uint32_t row0, uint32_t n_rows,
                    uint32_t col0, uint32_t n, float *__restrict__ cand_d, uint32_t *__restrict__ cand_i) {
-    __shared__ float s_d[WARPS][K];
-    __shared__ uint32_t s_i[WARPS][K];
+    __shared__ float s_d[RWARPS][K];
+    __shared__ uint32_t s_i[RWARPS][K];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t r = blockIdx.x * WARPS + warp;
+    const uint32_t r = blockIdx.x * RWARPS + warp;
     if (r >= n_rows || row0 + r >= n) return;
     const uint32_t grow = row0 + r;
     float *ld = s_d[warp];
@@ -199,33 +200,53 @@ int32_t build(rg_handle *h) {
     if (sc == 0)
         return rg_fail(h, RG_ERR_INVALID, "depth build: %u samples need %zu bytes of shared memory for the query rows alone (> 227 KB)",
                        S, tile_bytes);
-    RG_TRY(rg_reserve(h, h->sym_d, (size_t)B * C * sizeof(float)));
-    RG_TRY(rg_reserve(h, h->sym_t, (size_t)B * C * sizeof(float)));
+    const size_t buf_floats = (size_t)B * C;
+    RG_TRY(rg_reserve(h, h->sym_d, 2 * buf_floats * sizeof(float)));
+    RG_TRY(rg_reserve(h, h->sym_t, 2 * buf_floats * sizeof(float)));
+    for (auto &st : h->sym_stream)
+        if (!st) RG_CUDA(h, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto &ev : h->sym_ev)
+        if (!ev) RG_CUDA(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     auto kern = depth_tile_kernel<VARIANT>;
     RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     float *cd = (float *)h->cand_d.p;
     uint32_t *ci = (uint32_t *)h->cand_i.p;
-    float *Dm = (float *)h->sym_d.p, *Dt = (float *)h->sym_t.p;
+    cudaStream_t red = h->sym_stream[2];
+    cudaEvent_t *evaluated = h->sym_ev, *reduced = h->sym_ev + 2, fork = h->sym_ev[4];
     list_init_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(cd, ci, (uint64_t)n * K);
     h->tm.kernel_launches += 1;
+    RG_CUDA(h, cudaEventRecord(fork, h->stream));
+    for (auto &st : h->sym_stream) RG_CUDA(h, cudaStreamWaitEvent(st, fork, 0));
+    // Launch m evaluates into buffer m & 1 on evaluation stream m & 1, so the CTAs of launch m + 1 fill the SMs as
+    // those of launch m retire; the reducers of launch m follow on their own stream (in launch order: the lists need
+    // their candidates by increasing index) and release the buffer for launch m + 2.
+    uint32_t m = 0;
     for (uint32_t i0 = 0; i0 < n; i0 += B) {
         const uint32_t ni = std::min(B, n - i0), ni_pad = (ni + QB - 1) / QB * QB, i1 = i0 + ni;
-        for (uint32_t c0 = i0; c0 < n; c0 += C) {
+        for (uint32_t c0 = i0; c0 < n; c0 += C, ++m) {
             const uint32_t nc = std::min(C, n - c0), nc_pad = (nc + RG_TILE - 1) / RG_TILE * RG_TILE, c1 = c0 + nc;
             const uint32_t jb = std::max(c0, i1);          // first column right of the block
-            kern<<<ni_pad / QB, WARPS * 32, smem, h->stream>>>((const float4 *)h->cov_t.p, n, S, sc, i0, c0 / RG_TILE,
-                                                               nc_pad / RG_TILE, Dm, nc_pad, jb < c1 ? Dt : nullptr, ni_pad);
-            topk_reduce_kernel<K><<<(ni + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(Dm, nc_pad, nc_pad, i0, ni, c0,
-                                                                                         n, cd, ci);
+            float *Dm = (float *)h->sym_d.p + (m & 1) * buf_floats, *Dt = (float *)h->sym_t.p + (m & 1) * buf_floats;
+            cudaStream_t ev_st = h->sym_stream[m & 1];
+            if (m >= 2) RG_CUDA(h, cudaStreamWaitEvent(ev_st, reduced[m & 1], 0));
+            kern<<<ni_pad / QB, WARPS * 32, smem, ev_st>>>((const float4 *)h->cov_t.p, n, S, sc, i0, c0 / RG_TILE,
+                                                           nc_pad / RG_TILE, Dm, nc_pad, jb < c1 ? Dt : nullptr, ni_pad);
+            RG_CUDA(h, cudaEventRecord(evaluated[m & 1], ev_st));
+            RG_CUDA(h, cudaStreamWaitEvent(red, evaluated[m & 1], 0));
+            topk_reduce_kernel<K><<<(ni + RWARPS - 1) / RWARPS, RWARPS * 32, 0, red>>>(Dm, nc_pad, nc_pad, i0, ni, c0, n, cd, ci);
             h->tm.kernel_launches += 2;
             if (jb < c1) {
-                topk_reduce_kernel<K><<<(c1 - jb + WARPS - 1) / WARPS, WARPS * 32, 0, h->stream>>>(
+                topk_reduce_kernel<K><<<(c1 - jb + RWARPS - 1) / RWARPS, RWARPS * 32, 0, red>>>(
                     Dt + (size_t)(jb - c0) * ni_pad, ni_pad, ni_pad, jb, c1 - jb, i0, n, cd, ci);
                 h->tm.kernel_launches += 1;
             }
+            RG_CUDA(h, cudaEventRecord(reduced[m & 1], red));
         }
         RG_CUDA(h, cudaGetLastError());
     }
+    // join: everything the lists depend on ends on the reducer stream
+    RG_CUDA(h, cudaEventRecord(fork, red));
+    RG_CUDA(h, cudaStreamWaitEvent(h->stream, fork, 0));
     return RG_OK;
 }
 

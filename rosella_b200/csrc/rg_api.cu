@@ -89,6 +89,10 @@ void rg_destroy(rg_handle *h) {
     for (DevBuf *b : bufs) rg_release(*b);
     for (auto &ev : h->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto &ev : h->sym_ev)
+        if (ev) cudaEventDestroy(ev);
+    for (auto &st : h->sym_stream)
+        if (st) cudaStreamDestroy(st);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }

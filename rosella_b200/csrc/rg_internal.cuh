@@ -40,7 +40,9 @@ struct rg_handle {
     DevBuf cov_t;             // float4 (mean, var, ln var, +-1/(sd*sqrt2)) tile-major [tile][s][32]
     DevBuf err_flag;          // u32 device error word (non-finite coverage, ...)
     DevBuf cand_d, cand_i;    // select-phase candidates [rows][kprime]
-    DevBuf sym_d, sym_t;      // symmetric depth build: one block pair of distances and its transpose (knn_depth_sym.cu)
+    DevBuf sym_d, sym_t;      // symmetric depth build: two launches' worth of distances and their transposes (knn_depth_sym.cu)
+    cudaStream_t sym_stream[3] = {};   // two alternating evaluation streams + the reducer stream
+    cudaEvent_t sym_ev[5] = {};        // evaluated[2], reduced[2], fork
     DevBuf out_i, out_d, out_nv; // device staging of final lists for host-output calls
 
     // ---- TNF counting state
