@@ -31,10 +31,14 @@ tnf, cov, _ = synth.knn_tables(a.n, a.samples)
 ctx = gpu.Context(local)
 ctx.knn_load(tnf, cov)
 report = {"world": world, "n": a.n, "samples": a.samples, "k": a.k, "graphs": {}}
-for name, which in (("depth", gpu.GRAPH_DEPTH), ("tnf", gpu.GRAPH_TNF), ("tnf_euclid", gpu.GRAPH_TNF_EUCLID)):
+for name, which in (("depth", gpu.GRAPH_DEPTH), ("depth_symmetric", gpu.GRAPH_DEPTH), ("tnf", gpu.GRAPH_TNF),
+                    ("tnf_euclid", gpu.GRAPH_TNF_EUCLID)):
     torch.cuda.synchronize(); dist.barrier()
     t = time.perf_counter()
-    gi, gd = rdist.build_graph_distributed(ctx, which, a.k, a.n, rank, world)
+    if name == "depth_symmetric":      # block shares + all-to-all of partial lists + merge + all-gather
+        gi, gd = rdist.build_depth_graph_symmetric(ctx, a.k, a.n, rank, world)
+    else:                              # query-row shards + all-gather
+        gi, gd = rdist.build_graph_distributed(ctx, which, a.k, a.n, rank, world)
     torch.cuda.synchronize(); dist.barrier()
     dt = time.perf_counter() - t
     # every rank must hold the same gathered graph
@@ -43,7 +47,10 @@ for name, which in (("depth", gpu.GRAPH_DEPTH), ("tnf", gpu.GRAPH_TNF), ("tnf_eu
     dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     same_on_all_ranks = bool((lo == hi).all())
     if rank == 0:
+        if name == "depth_symmetric":
+            os.environ["RG_DEPTH_BUILD"] = "batch"          # the reference lists come from the batch kernel
         fi, fd, _ = ctx.knn_search(which, a.k)              # one GPU, all rows
+        os.environ.pop("RG_DEPTH_BUILD", None)
         report["graphs"][name] = {
             "seconds": dt, "same_on_all_ranks": same_on_all_ranks,
             "idx_equal_single_gpu": bool(np.array_equal(gi.cpu().numpy().astype(np.uint32), fi)),

@@ -118,6 +118,25 @@ int32_t rg_knn_search(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_begin
 int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_begin, uint64_t q_end,
                           uint32_t *idx_dev, float *dist_dev, uint32_t *n_valid_dev);
 
+/* A search of ALL rows of the coverage graph (q_begin = 0, q_end = n) evaluates each unordered pair once
+ * (the metric is symmetric up to a sign rule that is tracked, knn_depth_sym.cu); the lists are the same.
+ *
+ * The same whole-graph coverage build split over n_parts processes (one GPU each, tables loaded in all):
+ *   1. rg_knn_depth_partial_dev: part p evaluates its share of the row blocks against the rows to their right
+ *      and writes, for EVERY row, a K'-entry candidate list sorted by (distance, index) and padded with
+ *      (+inf, UINT32_MAX): cand_dist_dev / cand_idx_dev are device arrays [n][K'], K' = rg_knn_kprime(h, RG_GRAPH_DEPTH, k);
+ *   2. the host exchanges the lists so that the owner of rows [q_begin, q_end) holds all parts' lists of those
+ *      rows, [n_parts][q_end - q_begin][K'] (an all-to-all; rosella_b200/dist.py does it with NCCL);
+ *   3. rg_knn_depth_merge_dev merges them and finishes as rg_knn_search_dev does (f64 distances, same outputs).
+ * Both calls are asynchronous on rg_stream(h).  Replaces nothing in the reference by itself: it is how
+ * EmbedderEngine::build_mutual_kgraph (embedder.rs:31-86) scales past one GPU. */
+uint32_t rg_knn_kprime(rg_handle *h, uint32_t which, uint32_t k);
+int32_t rg_knn_depth_partial_dev(rg_handle *h, uint32_t k, uint32_t part, uint32_t n_parts,
+                                 float *cand_dist_dev, uint32_t *cand_idx_dev);
+int32_t rg_knn_depth_merge_dev(rg_handle *h, uint32_t k, uint32_t n_parts, const float *parts_dist_dev,
+                               const uint32_t *parts_idx_dev, uint64_t q_begin, uint64_t q_end,
+                               uint32_t *idx_dev, float *dist_dev, uint32_t *n_valid_dev);
+
 /* one call: load + search of all rows for the graphs in which_mask (bit RG_GRAPH_*);
  * outputs per graph may be NULL when its bit is clear. */
 int32_t rg_knn_build(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,

@@ -19,6 +19,7 @@ SYMBOLS = [
     "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
     "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
+    "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev",
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings",
 ]
 
@@ -71,6 +72,9 @@ def load() -> C.CDLL:
         "rg_knn_load": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
         "rg_knn_search": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, u32p, f32p, u32p]),
         "rg_knn_search_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, vp, vp, vp]),
+        "rg_knn_kprime": (C.c_uint32, [vp, C.c_uint32, C.c_uint32]),
+        "rg_knn_depth_partial_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
+        "rg_knn_depth_merge_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, vp, vp, C.c_uint64, C.c_uint64, vp, vp, vp]),
         "rg_knn_build": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                      C.c_uint32, u32p, f32p, u32p, f32p]),
         "rg_graph_mutual": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),

@@ -191,8 +191,11 @@ uint32_t chunk_cols(const rg_handle *h, uint32_t B) {
 // Block I = rows [i0, i0 + ni) is evaluated against the columns [i0, n) in chunks: its own square in full (both
 // orders of a pair inside the block are computed, B / 2N of the work) and everything to the right once.  Dm feeds the
 // lists of the block's rows, Dt those of the columns right of the block.
+//
+// part / n_parts: a process that holds one of n_parts GPUs takes every n_parts-th block in boustrophedon order (blocks
+// get cheaper to the right, so consecutive rounds run in opposite directions) and leaves PARTIAL lists for all rows.
 template <int VARIANT, int K>
-int32_t build(rg_handle *h) {
+int32_t build(rg_handle *h, float *cd, uint32_t *ci, uint32_t part, uint32_t n_parts) {
     const uint32_t n = (uint32_t)h->n, S = h->s, B = block_rows(h), C = chunk_cols(h, B);
     const size_t tile_bytes = (size_t)S * RG_TILE * sizeof(float4);
     size_t smem = 0;
@@ -209,8 +212,6 @@ int32_t build(rg_handle *h) {
         if (!ev) RG_CUDA(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     auto kern = depth_tile_kernel<VARIANT>;
     RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    float *cd = (float *)h->cand_d.p;
-    uint32_t *ci = (uint32_t *)h->cand_i.p;
     cudaStream_t red = h->sym_stream[2];
     cudaEvent_t *evaluated = h->sym_ev, *reduced = h->sym_ev + 2, fork = h->sym_ev[4];
     list_init_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(cd, ci, (uint64_t)n * K);
@@ -221,7 +222,9 @@ int32_t build(rg_handle *h) {
     // those of launch m retire; the reducers of launch m follow on their own stream (in launch order: the lists need
     // their candidates by increasing index) and release the buffer for launch m + 2.
     uint32_t m = 0;
-    for (uint32_t i0 = 0; i0 < n; i0 += B) {
+    for (uint32_t i0 = 0, blk = 0; i0 < n; i0 += B, ++blk) {
+        const uint32_t round = blk / n_parts, pos = blk % n_parts;
+        if (((round & 1) ? n_parts - 1 - pos : pos) != part) continue;
         const uint32_t ni = std::min(B, n - i0), ni_pad = (ni + QB - 1) / QB * QB, i1 = i0 + ni;
         for (uint32_t c0 = i0; c0 < n; c0 += C, ++m) {
             const uint32_t nc = std::min(C, n - c0), nc_pad = (nc + RG_TILE - 1) / RG_TILE * RG_TILE, c1 = c0 + nc;
@@ -251,13 +254,73 @@ int32_t build(rg_handle *h) {
 }
 
 template <int VARIANT>
-int32_t build_k(rg_handle *h, uint32_t kprime) {
+int32_t build_k(rg_handle *h, uint32_t kprime, float *cd, uint32_t *ci, uint32_t part, uint32_t n_parts) {
     switch (kprime) {
-        case 64: return build<VARIANT, 64>(h);
-        case 128: return build<VARIANT, 128>(h);
-        case 256: return build<VARIANT, 256>(h);
+        case 64: return build<VARIANT, 64>(h, cd, ci, part, n_parts);
+        case 128: return build<VARIANT, 128>(h, cd, ci, part, n_parts);
+        case 256: return build<VARIANT, 256>(h, cd, ci, part, n_parts);
     }
     return rg_fail(h, RG_ERR_INVALID, "depth build: unsupported K'=%u", kprime);
+}
+
+// Merge the n_parts partial lists of each row (pd / pi: [n_parts][q_count][K], each sorted by (distance, index), padded
+// with (inf, 0xffffffff)) into the row's K best.  No pair is held by two parts, so the final position of a candidate
+// is the number of candidates that precede it in (distance, index) order: one binary search per part.
+template <int K>
+__global__ void __launch_bounds__(RWARPS * 32)
+merge_lists_kernel(const float *__restrict__ pd, const uint32_t *__restrict__ pi, uint32_t n_parts, uint32_t q_count,
+                   float *__restrict__ cd, uint32_t *__restrict__ ci) {
+    extern __shared__ __align__(16) uint8_t msm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t r = blockIdx.x * RWARPS + warp, total = n_parts * K;
+    if (r >= q_count) return;
+    float *sd = reinterpret_cast<float *>(msm) + (size_t)warp * total;
+    uint32_t *si = reinterpret_cast<uint32_t *>(msm) + (size_t)RWARPS * total + (size_t)warp * total;
+    for (uint32_t c = lane; c < total; c += 32) {
+        const uint32_t p = c / K, e = c % K;
+        sd[c] = pd[((size_t)p * q_count + r) * K + e];
+        si[c] = pi[((size_t)p * q_count + r) * K + e];
+    }
+    for (int e = lane; e < K; e += 32) {
+        cd[(size_t)r * K + e] = INFINITY;
+        ci[(size_t)r * K + e] = 0xffffffffu;
+    }
+    __syncwarp();
+    for (uint32_t c = lane; c < total; c += 32) {
+        const float d = sd[c];
+        const uint32_t i = si[c];
+        if (i == 0xffffffffu) continue;
+        uint32_t rank = 0;
+        for (uint32_t p = 0; p < n_parts && rank < K; ++p) {
+            const float *ld = sd + p * K;
+            const uint32_t *li = si + p * K;
+            uint32_t lo = 0, hi = K;                  // first entry of part p not before (d, i)
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                const bool before = ld[mid] < d || (ld[mid] == d && li[mid] < i);
+                if (before) lo = mid + 1; else hi = mid;
+            }
+            rank += lo;
+        }
+        if (rank < K) {
+            cd[(size_t)r * K + rank] = d;
+            ci[(size_t)r * K + rank] = i;
+        }
+    }
+}
+
+template <int K>
+int32_t merge(rg_handle *h, uint32_t n_parts, const float *pd, const uint32_t *pi, uint64_t q_count) {
+    const size_t smem = (size_t)RWARPS * n_parts * K * 8;
+    if (smem > 227 * 1024)
+        return rg_fail(h, RG_ERR_INVALID, "depth merge: %u parts x K'=%d do not fit in shared memory", n_parts, K);
+    auto kern = merge_lists_kernel<K>;
+    RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)((q_count + RWARPS - 1) / RWARPS), RWARPS * 32, smem, h->stream>>>(
+        pd, pi, n_parts, (uint32_t)q_count, (float *)h->cand_d.p, (uint32_t *)h->cand_i.p);
+    RG_CUDA(h, cudaGetLastError());
+    h->tm.kernel_launches += 1;
+    return RG_OK;
 }
 
 }  // namespace
@@ -271,7 +334,19 @@ bool rg_depth_build_sym_wanted(const rg_handle *h) {
     return h->n > block_rows(h);
 }
 
-// cand_d / cand_i must hold n * kprime entries
-int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime) {
-    return h->variant == RG_VARIANT_FLIGHT ? build_k<RG_VARIANT_FLIGHT>(h, kprime) : build_k<RG_VARIANT_RUST>(h, kprime);
+// cd / ci: n * kprime entries on the device.  part == 0, n_parts == 1: the whole graph.
+int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime, float *cd, uint32_t *ci, uint32_t part, uint32_t n_parts) {
+    return h->variant == RG_VARIANT_FLIGHT ? build_k<RG_VARIANT_FLIGHT>(h, kprime, cd, ci, part, n_parts)
+                                           : build_k<RG_VARIANT_RUST>(h, kprime, cd, ci, part, n_parts);
+}
+
+// h->cand_d / cand_i (q_count * kprime entries) <- merged partial lists
+int32_t rg_launch_depth_merge(rg_handle *h, uint32_t kprime, uint32_t n_parts, const float *pd, const uint32_t *pi,
+                              uint64_t q_count) {
+    switch (kprime) {
+        case 64: return merge<64>(h, n_parts, pd, pi, q_count);
+        case 128: return merge<128>(h, n_parts, pd, pi, q_count);
+        case 256: return merge<256>(h, n_parts, pd, pi, q_count);
+    }
+    return rg_fail(h, RG_ERR_INVALID, "depth merge: unsupported K'=%u", kprime);
 }

@@ -193,7 +193,8 @@ int32_t launch_rescore(rg_handle *h, const double *data, uint32_t width, uint32_
 }  // namespace
 
 int32_t rg_launch_depth_select(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
-int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime);
+int32_t rg_launch_depth_build_sym(rg_handle *h, uint32_t kprime, float *cd, uint32_t *ci, uint32_t part, uint32_t n_parts);
+int32_t rg_launch_depth_merge(rg_handle *h, uint32_t kprime, uint32_t n_parts, const float *pd, const uint32_t *pi, uint64_t q_count);
 bool rg_depth_build_sym_wanted(const rg_handle *h);
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 uint32_t rg_tnf_kprime(const rg_handle *h, uint32_t k, uint32_t general);
@@ -226,7 +227,7 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
     RG_TRY(rg_reserve(h, h->cand_d, q_count * kprime * sizeof(float)));
     RG_TRY(rg_reserve(h, h->cand_i, q_count * kprime * sizeof(uint32_t)));
     RG_CUDA(h, cudaEventRecord(h->ev[3], h->stream));
-    if (which == RG_GRAPH_DEPTH && q_count == h->n && rg_depth_build_sym_wanted(h)) RG_TRY(rg_launch_depth_build_sym(h, kprime));
+    if (which == RG_GRAPH_DEPTH && q_count == h->n && rg_depth_build_sym_wanted(h)) RG_TRY(rg_launch_depth_build_sym(h, kprime, (float *)h->cand_d.p, (uint32_t *)h->cand_i.p, 0, 1));
     else if (which == RG_GRAPH_DEPTH) RG_TRY(rg_launch_depth_select(h, kprime, q_begin, q_count));
     else RG_TRY(rg_launch_tnf_select(h, which, kprime, q_begin, q_count));
     RG_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
@@ -244,5 +245,56 @@ extern "C" int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, u
     }
     RG_CUDA(h, cudaEventRecord(h->ev[5], h->stream));
     h->tm.select_ms = -1.0;   // resolved lazily by rg_get_timings (the launches above are asynchronous)
+    return RG_OK;
+}
+
+extern "C" uint32_t rg_knn_kprime(rg_handle *h, uint32_t which, uint32_t k) {
+    if (!h || k == 0) return 0;
+    uint32_t kprime = pick_kprime(k);
+    if (kprime && which != RG_GRAPH_DEPTH && h->n) kprime = rg_tnf_kprime(h, k, kprime);
+    return kprime;
+}
+
+extern "C" int32_t rg_knn_depth_partial_dev(rg_handle *h, uint32_t k, uint32_t part, uint32_t n_parts,
+                                            float *cand_dist_dev, uint32_t *cand_idx_dev) {
+    if (!h) return RG_ERR_INVALID;
+    if (h->n == 0 || !h->has_cov) return rg_fail(h, RG_ERR_STATE, "rg_knn_depth_partial: no coverage table loaded");
+    if (!cand_dist_dev || !cand_idx_dev) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_partial: output pointer is NULL");
+    if (n_parts == 0 || part >= n_parts) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_partial: part %u of %u", part, n_parts);
+    const uint32_t kprime = pick_kprime(k);
+    if (k == 0 || kprime == 0) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_partial: k=%u must be in [1,224]", k);
+    RG_CUDA(h, cudaSetDevice(h->device));
+    RG_CUDA(h, cudaEventRecord(h->ev[3], h->stream));
+    RG_TRY(rg_launch_depth_build_sym(h, kprime, cand_dist_dev, cand_idx_dev, part, n_parts));
+    RG_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
+    RG_CUDA(h, cudaEventRecord(h->ev[5], h->stream));
+    h->tm.select_ms = -1.0;
+    return RG_OK;
+}
+
+extern "C" int32_t rg_knn_depth_merge_dev(rg_handle *h, uint32_t k, uint32_t n_parts, const float *parts_dist_dev,
+                                          const uint32_t *parts_idx_dev, uint64_t q_begin, uint64_t q_end,
+                                          uint32_t *idx_dev, float *dist_dev, uint32_t *n_valid_dev) {
+    if (!h) return RG_ERR_INVALID;
+    if (h->n == 0 || !h->has_cov) return rg_fail(h, RG_ERR_STATE, "rg_knn_depth_merge: no coverage table loaded");
+    if (!parts_dist_dev || !parts_idx_dev || !idx_dev || !dist_dev) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_merge: NULL pointer");
+    if (q_begin > q_end || q_end > h->n) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_merge: query range outside [0,n)");
+    if (n_parts == 0) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_merge: n_parts = 0");
+    const uint32_t kprime = pick_kprime(k);
+    if (k == 0 || kprime == 0) return rg_fail(h, RG_ERR_INVALID, "rg_knn_depth_merge: k=%u must be in [1,224]", k);
+    const uint64_t q_count = q_end - q_begin;
+    if (q_count == 0) return RG_OK;
+    RG_CUDA(h, cudaSetDevice(h->device));
+    RG_TRY(rg_reserve(h, h->cand_d, q_count * kprime * sizeof(float)));
+    RG_TRY(rg_reserve(h, h->cand_i, q_count * kprime * sizeof(uint32_t)));
+    RG_CUDA(h, cudaEventRecord(h->ev[3], h->stream));
+    RG_TRY(rg_launch_depth_merge(h, kprime, n_parts, parts_dist_dev, parts_idx_dev, q_count));
+    RG_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
+    const double *data = (const double *)h->cov64.p;
+    RG_TRY(h->variant == RG_VARIANT_FLIGHT
+               ? (launch_rescore<RG_VARIANT_FLIGHT, RG_GRAPH_DEPTH>(h, data, 2 * h->s, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev))
+               : (launch_rescore<RG_VARIANT_RUST, RG_GRAPH_DEPTH>(h, data, 2 * h->s, kprime, k, q_begin, q_count, idx_dev, dist_dev, n_valid_dev)));
+    RG_CUDA(h, cudaEventRecord(h->ev[5], h->stream));
+    h->tm.select_ms = -1.0;
     return RG_OK;
 }

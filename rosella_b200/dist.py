@@ -49,5 +49,51 @@ def build_graph_distributed(ctx, which: int, k: int, n: int, rank: int, world: i
     return idx, dst
 
 
+def exchange_partial_lists(part_d, part_i, n: int, rank: int, world: int, group=None):
+    """The exchange step of the symmetric whole-graph coverage build.  Every rank holds partial candidate lists for
+    ALL rows ([n, K'] distances and indices); the owner of a row shard needs every rank's lists of its rows.  One
+    all-to-all per array: rank r sends rows shard_range(n, q, world) to rank q.
+    -> ([world, rows_of_this_shard, K'] distances, same for indices), the layout rg_knn_depth_merge_dev reads."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return part_d.unsqueeze(0), part_i.unsqueeze(0)
+    sizes = [shard_range(n, r, world)[1] - shard_range(n, r, world)[0] for r in range(world)]
+    mine = sizes[rank]
+    out = []
+    for t in (part_d, part_i):
+        recv = torch.empty((world * mine,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_to_all_single(recv, t.contiguous(), output_split_sizes=[mine] * world, input_split_sizes=sizes, group=group)
+        out.append(recv.view((world, mine) + tuple(t.shape[1:])))
+    return out[0], out[1]
+
+
+def build_depth_graph_symmetric(ctx, k: int, n: int, rank: int, world: int):
+    """Whole coverage graph on `world` GPUs with each unordered pair evaluated once: this rank's share
+    of the row blocks (rg_knn_depth_partial_dev) -> all-to-all of the partial lists -> merge + f64 distances of this
+    rank's row shard (rg_knn_depth_merge_dev) -> all-gather.  -> (idx int32 [n,k], dist float32 [n,k]) on the device."""
+    import torch
+    from . import gpu
+    dev = torch.device("cuda", ctx.device)
+    kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
+    qb, qe = shard_range(n, rank, world)
+    part_d = torch.empty((n, kp), dtype=torch.float32, device=dev)
+    part_i = torch.empty((n, kp), dtype=torch.int32, device=dev)
+    idx = torch.empty((qe - qb, k), dtype=torch.int32, device=dev)
+    dst = torch.empty((qe - qb, k), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize(dev)      # the buffers above come from torch's stream; the work below runs on ctx.stream
+    ctx.knn_depth_partial_dev(k, rank, world, part_d.data_ptr(), part_i.data_ptr())
+    ext = torch.cuda.ExternalStream(ctx.stream, device=ctx.device)
+    with torch.cuda.stream(ext):
+        all_d, all_i = exchange_partial_lists(part_d, part_i, n, rank, world)
+        if qe > qb:
+            ctx.knn_depth_merge_dev(k, world, all_d.data_ptr(), all_i.data_ptr(), qb, qe, idx.data_ptr(), dst.data_ptr())
+        if world > 1:
+            idx = all_gather_rows(idx, n, world)
+            dst = all_gather_rows(dst, n, world)
+    ctx.sync()
+    return idx, dst
+
+
 def concat_host(parts: list[np.ndarray]) -> np.ndarray:
     return np.concatenate(parts, axis=0)

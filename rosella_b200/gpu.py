@@ -148,6 +148,20 @@ class Context:
         """Outputs are raw device addresses (e.g. torch tensor .data_ptr()); asynchronous on self.stream."""
         self._chk(self.lib.rg_knn_search_dev(self.h, which, k, q_begin, q_end, idx_ptr, dist_ptr, nvalid_ptr or None))
 
+    def knn_kprime(self, which: int, k: int) -> int:
+        return int(self.lib.rg_knn_kprime(self.h, which, k))
+
+    def knn_depth_partial_dev(self, k: int, part: int, n_parts: int, cand_dist_ptr: int, cand_idx_ptr: int):
+        """This part's share of the symmetric whole-graph coverage build: partial K' lists for every row, device
+        arrays [n][K'] (K' = knn_kprime(GRAPH_DEPTH, k)); asynchronous on self.stream."""
+        self._chk(self.lib.rg_knn_depth_partial_dev(self.h, k, part, n_parts, cand_dist_ptr, cand_idx_ptr))
+
+    def knn_depth_merge_dev(self, k: int, n_parts: int, parts_dist_ptr: int, parts_idx_ptr: int, q_begin: int, q_end: int,
+                            idx_ptr: int, dist_ptr: int, nvalid_ptr: int = 0):
+        """Merge [n_parts][q_end - q_begin][K'] partial lists and finish them like knn_search_dev."""
+        self._chk(self.lib.rg_knn_depth_merge_dev(self.h, k, n_parts, parts_dist_ptr, parts_idx_ptr, q_begin, q_end,
+                                                  idx_ptr, dist_ptr, nvalid_ptr or None))
+
     def knn_build(self, tnf, cov, k: int, variant: int = VARIANT_RUST, which_mask: int = 3):
         tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
         n = (tnf if tnf is not None else cov).shape[0]
