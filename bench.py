@@ -36,6 +36,8 @@ def parse_args():
     ap.add_argument("--k", type=int, default=30)
     ap.add_argument("--query-rows", type=int, default=0, help="query rows per GPU per step (0 = 2 waves of CTAs)")
     ap.add_argument("--tnf-gbp", type=float, default=-1.0, help="TNF counting set in Gbp (-1 = auto, 0 = skip)")
+    ap.add_argument("--whole-graph-rows", type=int, default=200_000,
+                    help="rows of the whole-graph coverage build timed beside the step (N=1 only; 0 = skip)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -161,6 +163,29 @@ def main_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def whole_graph(ctx, cov, rows, k):
+    """The drop-in call is a build of ALL rows (rg_knn_build): the coverage graph then takes the symmetric block path
+    (knn_depth_sym.cu, every unordered pair once).  Timed here on the first `rows` rows of the step's table, beside the
+    batch kernel on the same rows, with the lists compared bit for bit."""
+    import time
+    from rosella_b200 import gpu
+    ctx.knn_load(None, cov[:rows], gpu.VARIANT_RUST)
+    out = {"workload": f"coverage graph of all {rows} rows x {cov.shape[1] // 2} samples, k={k}, one GPU, host lists returned"}
+    res = {}
+    for mode in ("batch", "symmetric"):
+        os.environ["RG_DEPTH_BUILD"] = "batch" if mode == "batch" else "sym"
+        ctx.sync()
+        t0 = time.perf_counter()
+        res[mode] = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+        out[f"{mode}_s"] = time.perf_counter() - t0
+        out[f"{mode}_select_ms"] = ctx.timings()["select_ms"]
+    os.environ.pop("RG_DEPTH_BUILD", None)
+    out["identical"] = bool(np.array_equal(res["batch"][0], res["symmetric"][0]) and np.array_equal(res["batch"][1], res["symmetric"][1]))
+    out["contigs_per_s_symmetric"] = rows / out["symmetric_s"]
+    out["contigs_per_s_batch"] = rows / out["batch_s"]
+    return out
+
+
 def main_ours(args):
     from benchmarks import cpu_arm, knn_arm, tnf_arm
     helpers = sys.modules[__name__]
@@ -208,6 +233,8 @@ def main_ours(args):
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()
                                     if k in ("value", "unit", "cores", "kind", "sample")}
+        if args.whole_graph_rows > 0:
+            line["whole_graph"] = whole_graph(r["ctx"], cov, min(args.whole_graph_rows, args.n), args.k)
         gbp = args.tnf_gbp
         if gbp < 0:
             import psutil

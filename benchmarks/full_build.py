@@ -1,8 +1,9 @@
 #!/usr/bin/env python
-"""One COMPLETE kNN build (both graphs, all n query rows) on one GPU through the host-buffer C ABI, plus a
-sampled parity check against the exhaustive f64 oracle (a fixed random sample of query rows
-against ALL n references).  Writes one JSON object.
-  python benchmarks/full_build.py [--n 1000000] [--samples 50] [--k 30] [--check-rows 128] [--out file]"""
+"""Whole-graph build of BASELINE.json configs[2] on N GPUs (torchrun, NCCL; N = 1 runs without a process group):
+coverage graph by the symmetric block build (all-to-all of partial lists) and by query-row shards, TNF graph by
+query-row shards.  Times are device-synchronised wall clock, max over ranks.  One JSON line on rank 0.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
+      benchmarks/full_build.py [--rows 1000000] [--samples 50] [--k 30] [--skip-row-shards]"""
 import argparse
 import json
 import os
@@ -11,55 +12,60 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
 
-import oracle  # noqa: E402  (checker only)
+from rosella_b200 import dist as rdist  # noqa: E402
 from rosella_b200 import gpu, synth  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, default=1_000_000)
+ap.add_argument("--rows", dest="n", type=int, default=1_000_000)
 ap.add_argument("--samples", type=int, default=50)
 ap.add_argument("--k", type=int, default=30)
-ap.add_argument("--check-rows", type=int, default=128)
-ap.add_argument("--out", default="gpurun_out/full_build.json")
+ap.add_argument("--skip-row-shards", action="store_true")
 a = ap.parse_args()
-
+rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 tnf, cov, _ = synth.knn_tables(a.n, a.samples)
-ctx = gpu.Context(0)
-t0 = time.perf_counter()
+ctx = gpu.Context(local)
 ctx.knn_load(tnf, cov)
-t_load = time.perf_counter() - t0
-res = {}
-times = {}
-for name, which in (("depth", gpu.GRAPH_DEPTH), ("tnf", gpu.GRAPH_TNF)):
-    t = time.perf_counter()
-    res[name] = ctx.knn_search(which, a.k)
-    times[name] = time.perf_counter() - t
-    tm = ctx.timings()
-    times[name + "_select_ms"] = tm["select_ms"]
-    times[name + "_rescore_ms"] = tm["rescore_ms"]
-total = time.perf_counter() - t0
 
-rng = np.random.default_rng(123)
-rows = np.sort(rng.choice(a.n, a.check_rows, replace=False)).astype(np.uint64)
-check = {}
-for name, which, data in (("depth", oracle.DEPTH, cov), ("tnf", oracle.TNF, tnf)):
+
+def timed(fn):
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     t = time.perf_counter()
-    oi, od, _ = oracle.knn(data, which, a.k, oracle.RUST, qrows=rows)
-    idx, dist, nv = res[name]
-    gi, gd = idx[rows], dist[rows]
-    kth = od[:, -1:]
-    # tie-aware recall: an oracle neighbour is found if present, or if it ties the k-th distance
-    found = np.array([[(oi[r, j] in set(gi[r].tolist())) or od[r, j] >= kth[r, 0] * (1 - 2.4e-7) for j in range(a.k)]
-                      for r in range(len(rows))])
-    same = gi == oi
-    rel = np.abs(gd[same] - od[same]) / np.maximum(np.abs(od[same]), 1e-30)
-    check[name] = {"rows": int(len(rows)), "recall_tie_aware": float(found.mean()), "position_exact": float(same.mean()),
-                   "max_rel_dist_err_on_matches": float(rel.max()) if rel.size else 0.0,
-                   "kth_max_rel_err": float((np.abs(gd[:, -1] - od[:, -1]) / od[:, -1]).max()),
-                   "oracle_seconds": time.perf_counter() - t}
-out = {"n": a.n, "samples": a.samples, "k": a.k, "load_s": t_load, "seconds": times, "total_s": total,
-       "contigs_per_s": a.n / total, "parity_sample": check, "n_valid_min": int(min(res["depth"][2].min(), res["tnf"][2].min()))}
-os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
-json.dump(out, open(a.out, "w"), indent=1)
-print(json.dumps(out))
+    out = fn()
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t], device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    return out, float(dt)
+
+
+report = {"world": world, "n": a.n, "samples": a.samples, "k": a.k}
+if world > 1:       # warm the communicators outside the timed regions
+    timed(lambda: rdist.all_gather_rows(torch.zeros((rdist.shard_range(a.n, rank, world)[1] - rdist.shard_range(a.n, rank, world)[0], 2), device="cuda"), a.n, world))
+(si, sd), t_sym = timed(lambda: rdist.build_depth_graph_symmetric(ctx, a.k, a.n, rank, world))
+report["depth_symmetric_s"] = round(t_sym, 3)
+if not a.skip_row_shards:
+    os.environ["RG_DEPTH_BUILD"] = "batch"
+    (bi, bd), t_rows = timed(lambda: rdist.build_graph_distributed(ctx, gpu.GRAPH_DEPTH, a.k, a.n, rank, world))
+    os.environ.pop("RG_DEPTH_BUILD")
+    report["depth_row_shards_s"] = round(t_rows, 3)
+    report["depth_lists_identical"] = bool(torch.equal(si, bi) and torch.equal(sd, bd))
+(ti, td), t_tnf = timed(lambda: rdist.build_graph_distributed(ctx, gpu.GRAPH_TNF, a.k, a.n, rank, world))
+report["tnf_row_shards_s"] = round(t_tnf, 3)
+report["graph_s"] = round(t_sym + t_tnf, 3)
+report["contigs_per_s"] = round(a.n / (t_sym + t_tnf), 1)
+if rank == 0:
+    print(json.dumps(report), flush=True)
+if world > 1:
+    dist.barrier()
+ctx.close()
+if world > 1:
+    dist.destroy_process_group()
+sys.exit(0)

@@ -3,7 +3,7 @@
 rg_knn_search_dev, the slabs are all-gathered over NVLink, and the gathered lists must equal, bit for bit, the
 lists one GPU computes for all rows.
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-      benchmarks/multi_gpu_check.py [--n 20000] [--samples 10] [--k 30]"""
+      benchmarks/multi_gpu_check.py [--rows 20000] [--samples 10] [--k 30]"""
 import argparse
 import json
 import os
@@ -20,7 +20,7 @@ from rosella_b200 import dist as rdist  # noqa: E402
 from rosella_b200 import gpu, synth  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, default=20000)
+ap.add_argument("--rows", dest="n", type=int, default=20000)
 ap.add_argument("--samples", type=int, default=10)
 ap.add_argument("--k", type=int, default=30)
 a = ap.parse_args()
