@@ -47,7 +47,9 @@ def timed(fn):
 
 
 report = {"world": world, "n": a.n, "samples": a.samples, "k": a.k}
-if world > 1:       # warm the communicators outside the timed regions
+if world > 1:       # warm the communicators (all-gather ring, all-to-all peer connections) outside the timed regions
+    kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, a.k)
+    timed(lambda: rdist.exchange_partial_lists(torch.zeros((a.n, kp), device="cuda"), torch.zeros((a.n, kp), dtype=torch.int32, device="cuda"), a.n, rank, world))
     timed(lambda: rdist.all_gather_rows(torch.zeros((rdist.shard_range(a.n, rank, world)[1] - rdist.shard_range(a.n, rank, world)[0], 2), device="cuda"), a.n, world))
 (si, sd), t_sym = timed(lambda: rdist.build_depth_graph_symmetric(ctx, a.k, a.n, rank, world))
 report["depth_symmetric_s"] = round(t_sym, 3)
