@@ -163,24 +163,42 @@ def main_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def whole_graph(ctx, cov, rows, k):
+def whole_graph(ctx, cov, rows, k, rank=0, world=1):
     """The drop-in call is a build of ALL rows (rg_knn_build): the coverage graph then takes the symmetric block path
-    (knn_depth_sym.cu, every unordered pair once).  Timed here on the first `rows` rows of the step's table, beside the
-    batch kernel on the same rows, with the lists compared bit for bit."""
+    (knn_depth_sym.cu, every unordered pair once; on N GPUs block shares + all-to-all of partial lists).
+    Timed here on the first `rows` rows of the step's table, beside the batch kernel / query-row shards on the same
+    rows, with the lists compared bit for bit.  Collective: every rank calls it."""
     import time
-    from rosella_b200 import gpu
+    import torch
+    from rosella_b200 import dist as rdist, gpu
     ctx.knn_load(None, cov[:rows], gpu.VARIANT_RUST)
-    out = {"workload": f"coverage graph of all {rows} rows x {cov.shape[1] // 2} samples, k={k}, one GPU, host lists returned"}
+    out = {"workload": f"coverage graph of all {rows} rows x {cov.shape[1] // 2} samples, k={k}, {world} GPU(s)"}
     res = {}
+    if world > 1:       # peer connections of the all-to-all are set up outside the timed region
+        kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
+        rdist.exchange_partial_lists(torch.zeros((rows, kp), device="cuda"), torch.zeros((rows, kp), dtype=torch.int32, device="cuda"), rows, rank, world)
     for mode in ("batch", "symmetric"):
         os.environ["RG_DEPTH_BUILD"] = "batch" if mode == "batch" else "sym"
-        ctx.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
         t0 = time.perf_counter()
-        res[mode] = ctx.knn_search(gpu.GRAPH_DEPTH, k)
-        out[f"{mode}_s"] = time.perf_counter() - t0
-        out[f"{mode}_select_ms"] = ctx.timings()["select_ms"]
+        if world == 1:
+            res[mode] = ctx.knn_search(gpu.GRAPH_DEPTH, k)[:2]       # host lists returned
+        elif mode == "batch":
+            res[mode] = rdist.build_graph_distributed(ctx, gpu.GRAPH_DEPTH, k, rows, rank, world)
+        else:
+            res[mode] = rdist.build_depth_graph_symmetric(ctx, k, rows, rank, world)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+        out[f"{mode}_s"] = float(dt)
+        if world == 1:
+            out[f"{mode}_select_ms"] = ctx.timings()["select_ms"]
     os.environ.pop("RG_DEPTH_BUILD", None)
-    out["identical"] = bool(np.array_equal(res["batch"][0], res["symmetric"][0]) and np.array_equal(res["batch"][1], res["symmetric"][1]))
+    same = (np.array_equal if world == 1 else torch.equal)
+    out["identical"] = bool(same(res["batch"][0], res["symmetric"][0]) and same(res["batch"][1], res["symmetric"][1]))
     out["contigs_per_s_symmetric"] = rows / out["symmetric_s"]
     out["contigs_per_s_batch"] = rows / out["batch_s"]
     return out
@@ -229,12 +247,12 @@ def main_ours(args):
         "microbench": micro,
     }
     tnf, cov = r["tables"]
+    if r.get("whole_graph"):
+        line["whole_graph"] = r["whole_graph"]
     if world == 1:
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()
                                     if k in ("value", "unit", "cores", "kind", "sample")}
-        if args.whole_graph_rows > 0:
-            line["whole_graph"] = whole_graph(r["ctx"], cov, min(args.whole_graph_rows, args.n), args.k)
         gbp = args.tnf_gbp
         if gbp < 0:
             import psutil

@@ -126,6 +126,10 @@ def run(args, helpers):
         dist.all_reduce(t_loc, op=dist.ReduceOp.MAX)
     total_ms, e2e_total_ms = float(t_loc[0]), float(t_loc[1])
 
+    wg = None
+    if args.whole_graph_rows > 0:
+        wg = helpers.whole_graph(ctx, cov, min(args.whole_graph_rows, n), k, rank, world)
+
     absent_all = (cov[:, 0::2] <= 0).sum(axis=0).astype(np.float64)
     flops_depth = helpers.algorithmic_flops(cov[qb:qe], absent_all, n, graphs_tnf=0)
     flops_tnf = float(q_rows) * n * 272.0
@@ -136,6 +140,6 @@ def run(args, helpers):
         "tnf_res_ms": tnf_res_ms, "flops_depth": flops_depth, "flops_tnf": flops_tnf,
         "h2d_per_step": int(h2d_per_step), "d2h_per_step": int(d2h_per_step), "gen_s": gen_s,
         "load_h2d_ms": load_t["h2d_ms"], "load_transform_ms": load_t["transform_ms"],
-        "tables": (tnf, cov), "ctx": ctx,
+        "tables": (tnf, cov), "ctx": ctx, "whole_graph": wg,
     }
     return result

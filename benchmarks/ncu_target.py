@@ -20,6 +20,7 @@ ap.add_argument("--rows", type=int, default=9472)
 ap.add_argument("--k", type=int, default=30)
 ap.add_argument("--gbp", type=float, default=0.3)
 ap.add_argument("--passes", type=int, default=2)
+ap.add_argument("--sym-rows", type=int, default=0, help="then a whole-graph (symmetric) coverage build of this many rows")
 a = ap.parse_args()
 
 import torch  # noqa: E402
@@ -46,4 +47,8 @@ for p in range(a.passes):
     print(f"pass {p}: depth_select {t1['select_ms']:.3f} ms rescore {t1['rescore_ms']:.3f} ms | tnf_select {t2['select_ms']:.3f} ms "
           f"rescore {t2['rescore_ms']:.3f} ms | tnf_count packed {t3['tnf_count_ms']:.3f} ms ascii {t4['tnf_count_ms']:.3f} ms "
           f"({int(offs[-1])} bp)")
+if a.sym_rows:
+    ctx.knn_load(None, cov[:a.sym_rows])
+    ctx.knn_search(gpu.GRAPH_DEPTH, a.k)
+    print(f"symmetric build of {a.sym_rows} rows: select {ctx.timings()['select_ms']:.3f} ms")
 ctx.close()
