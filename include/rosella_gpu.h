@@ -143,6 +143,19 @@ int32_t rg_knn_build(rg_handle *h, const double *tnf, const double *cov, uint64_
                      uint32_t s, uint32_t k, uint32_t variant, uint32_t which_mask,
                      uint32_t *tnf_idx, float *tnf_dist, uint32_t *depth_idx, float *depth_dist);
 
+/* EmbedderEngine::build_mutual_kgraph (src/embedding/embedder.rs:31-86) in one call with its two filters APPLIED on
+ * the device (the reference computes them and drops the result, nearest_neighbour_graph.rs:33,:70):
+ *   kgraph = intersect(depth_kgraph, tnf_kgraph, max(keep_n_edges, 5))   (embedder.rs:68)
+ *   kgraph = mutual_knn(kgraph, keep_n_edges)                            (embedder.rs:69)
+ * Result as CSR in HOST memory: offsets[n+1]; neighbours / weights (capacity n*k each) hold node i's surviving edges
+ * at [offsets[i], offsets[i+1]) in list order (ascending coverage distance, f32 of the f64 metric);
+ * disconnected (capacity n, may be NULL) lists the nodes left without edges in ascending order
+ * (embedder.rs:72-84), *n_disconnected their number. */
+int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                            uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges,
+                            uint64_t *offsets, uint32_t *neighbours, float *weights,
+                            uint64_t *n_disconnected, uint32_t *disconnected);
+
 /* ------------------------------------------------------------------ graph post-ops */
 /* keep[i*k+j] = 1 when edge j of node i survives mutual_knn / intersect
  * (nearest_neighbour_graph.rs:12-35 / :38-72; the reference computes these lists and then drops

@@ -147,5 +147,27 @@ def intersect(base: np.ndarray, other: np.ndarray, keep_n_edges: int) -> np.ndar
     return keep
 
 
+def build_mutual_kgraph(depth_idx, depth_dist, tnf_idx, keep_n_edges: int):
+    """EmbedderEngine::build_mutual_kgraph's post-processing (embedder.rs:68-84) with the filters applied:
+    intersect(depth, tnf, max(keep_n_edges, 5)) then mutual_knn(., keep_n_edges) on the filtered lists.
+    -> (offsets u64[n+1], neighbours u32, weights f32, disconnected u32)"""
+    PAD = 0xFFFFFFFF
+    depth_idx = np.ascontiguousarray(depth_idx, np.uint32)
+    n, k = depth_idx.shape
+    keep1 = intersect(depth_idx, tnf_idx, max(keep_n_edges, 5)).astype(bool)
+    f_idx = np.full((n, k), PAD, np.uint32)                 # the filtered lists, compacted to the left
+    f_dist = np.zeros((n, k), np.float32)
+    for i in range(n):
+        m = keep1[i]
+        c = int(m.sum())
+        f_idx[i, :c] = depth_idx[i][m]
+        f_dist[i, :c] = depth_dist[i][m]
+    keep2 = mutual_knn(f_idx, keep_n_edges).astype(bool)
+    counts = keep2.sum(axis=1).astype(np.uint64)
+    offsets = np.zeros(n + 1, np.uint64)
+    offsets[1:] = np.cumsum(counts)
+    return offsets, f_idx[keep2], f_dist[keep2], np.where(counts == 0)[0].astype(np.uint32)
+
+
 def max_threads() -> int:
     return lib().orc_max_threads()

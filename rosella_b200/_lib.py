@@ -19,7 +19,7 @@ SYMBOLS = [
     "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
     "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
-    "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev",
+    "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings",
 ]
 
@@ -77,6 +77,8 @@ def load() -> C.CDLL:
         "rg_knn_depth_merge_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, vp, vp, C.c_uint64, C.c_uint64, vp, vp, vp]),
         "rg_knn_build": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                      C.c_uint32, u32p, f32p, u32p, f32p]),
+        "rg_knn_build_mutual": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                            C.c_uint32, C.POINTER(C.c_uint64), u32p, f32p, C.POINTER(C.c_uint64), u32p]),
         "rg_graph_mutual": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),

@@ -148,6 +148,20 @@ class Context:
         """Outputs are raw device addresses (e.g. torch tensor .data_ptr()); asynchronous on self.stream."""
         self._chk(self.lib.rg_knn_search_dev(self.h, which, k, q_begin, q_end, idx_ptr, dist_ptr, nvalid_ptr or None))
 
+    def knn_build_mutual(self, tnf, cov, k: int, keep_n_edges: int, variant: int = VARIANT_RUST):
+        """build_mutual_kgraph with the filters applied -> (offsets u64[n+1], neighbours u32[E], weights f32[E],
+        disconnected u32[...])"""
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        n, d, s = tnf.shape[0], tnf.shape[1], cov.shape[1] // 2
+        off = np.zeros(n + 1, np.uint64)
+        nbr, w = np.zeros(n * k, np.uint32), np.zeros(n * k, np.float32)
+        disc, nd = np.zeros(n, np.uint32), C.c_uint64(0)
+        self._chk(self.lib.rg_knn_build_mutual(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, k,
+                                               variant, keep_n_edges, _lib.ptr(off, C.c_uint64), _lib.ptr(nbr, C.c_uint32),
+                                               _lib.ptr(w, C.c_float), C.byref(nd), _lib.ptr(disc, C.c_uint32)))
+        e = int(off[-1])
+        return off, nbr[:e].copy(), w[:e].copy(), disc[:nd.value].copy()
+
     def knn_kprime(self, which: int, k: int) -> int:
         return int(self.lib.rg_knn_kprime(self.h, which, k))
 

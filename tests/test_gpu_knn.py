@@ -241,6 +241,22 @@ def test_graph_ops(ctx):
         assert np.array_equal(ctx.graph_intersect(di, ti, keep_n), oracle.intersect(di, ti, keep_n))
 
 
+@pytest.mark.parametrize("keep_n_edges", [0, 3, 8, 12])
+def test_build_mutual_kgraph_on_device(ctx, keep_n_edges):
+    """rg_knn_build_mutual (intersect + mutual_knn applied on the device, CSR out) against the oracle's restatement of
+    embedder.rs:68-84 fed with the lists of rg_knn_build."""
+    tnf, cov, _ = synth.knn_tables(1200, 3, seed=12)
+    (ti, _), (di, dd) = ctx.knn_build(tnf, cov, 12)
+    off, nbr, w, disc = ctx.knn_build_mutual(tnf, cov, 12, keep_n_edges)
+    o_off, o_nbr, o_w, o_disc = oracle.build_mutual_kgraph(di, dd, ti, keep_n_edges)
+    assert np.array_equal(off, o_off) and np.array_equal(nbr, o_nbr) and np.array_equal(w, o_w)
+    assert np.array_equal(disc, o_disc)
+    if keep_n_edges == 0:
+        assert 0 < off[-1] < di.size                  # the filters did drop edges
+    if keep_n_edges >= 12:
+        assert off[-1] == di.size and len(disc) == 0
+
+
 def test_config1_full_build_100k(ctx):
     """BASELINE.json configs[1]: 100k contigs x (136 TNF + 10 samples), k = 30, the whole graph on one B200 through
     rg_knn_build; three blocks of rows are checked against the exhaustive f64 oracle, all rows against the

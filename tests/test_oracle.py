@@ -121,3 +121,25 @@ def test_graph_ops():
     assert oracle.mutual_knn(idx, 1).tolist() == [[1, 0], [1, 1], [1, 0]]
     other = np.array([[2, 1], [2, 0xFFFFFFFF], [0, 1]], np.uint32)
     assert oracle.intersect(idx, other, 0).tolist() == [[0, 1], [1, 1], [1, 0]]
+
+
+def test_build_mutual_kgraph_restatement_matches_list_semantics():
+    """oracle.build_mutual_kgraph against a literal list-of-lists walk of embedder.rs:68-84 /
+    nearest_neighbour_graph.rs:12-72 with the commented-out assignments (:33, :70) applied."""
+    from rosella_b200 import synth
+    tnf, cov, _ = synth.knn_tables(120, 3, seed=4)
+    k = 8
+    di, dd, _ = oracle.knn(cov, oracle.DEPTH, k)
+    ti, _, _ = oracle.knn(tnf, oracle.TNF, k)
+    depth = [[(int(j), float(w)) for j, w in zip(di[i], dd[i])] for i in range(120)]
+    tnf_l = [[int(j) for j in ti[i]] for i in range(120)]
+    for keep_n_edges in (0, 2, 6, 8):
+        keep_first = max(keep_n_edges, 5)
+        inter = [[e for p, e in enumerate(nb) if p < keep_first or node in tnf_l[e[0]]] for node, nb in enumerate(depth)]
+        mutual = [[e for p, e in enumerate(nb) if p < keep_n_edges or any(r[0] == node for r in inter[e[0]])]
+                  for node, nb in enumerate(inter)]
+        off, nbr, w, disc = oracle.build_mutual_kgraph(di, dd, ti, keep_n_edges)
+        assert [int(off[i + 1] - off[i]) for i in range(120)] == [len(m) for m in mutual]
+        assert nbr.tolist() == [e[0] for m in mutual for e in m]
+        assert np.array_equal(w, np.array([e[1] for m in mutual for e in m], np.float32))
+        assert disc.tolist() == [i for i, m in enumerate(mutual) if not m]
