@@ -110,6 +110,36 @@ def peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1647.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(kernel: str, grid: str | None = None):
+    """DRAM bytes per launch (read + write) of `kernel` from the newest committed `ncu --set full` summary under
+    profiles/ (benchmarks/ncu_summary.py); `grid` restricts to a launch of that grid size.  -> (bytes, file) or (None, None)"""
+    import glob
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    for path in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_ncu_full_summary.json")), reverse=True):
+        try:
+            doc = json.load(open(path))
+            kernels = doc.get("kernels", []) if isinstance(doc, dict) else doc
+        except (OSError, ValueError):
+            continue
+        for rec in kernels:
+            if kernel not in rec.get("Kernel Name", "") or (grid and rec.get("Grid Size") != grid):
+                continue
+            total, ok = 0.0, 0
+            for key, val in rec.items():
+                if key.startswith(("dram__bytes_read.sum", "dram__bytes_write.sum")):
+                    unit = key[key.index("[") + 1:-1] if "[" in key else "byte"
+                    try:
+                        v = float(val)
+                    except ValueError:
+                        continue
+                    if v == v and unit in scale:
+                        total += v * scale[unit]
+                        ok += 1
+            if ok == 2:
+                return total, os.path.basename(path)
+    return None, None
+
+
 def fp32_peak_tflops():
     """Live FFMA micro-benchmark (rosella_b200/build/microbench); MEASURED_PEAKS.json has no FP32 entry."""
     exe = os.path.join(ROOT, "rosella_b200", "build", "microbench")
@@ -217,6 +247,8 @@ def main_ours(args):
     pk = peaks()
     fp32, micro = fp32_peak_tflops()
     ach = r["flops_depth"] / (r["depth_sel_ms"] * 1e-3) / 1e12
+    grid = f"({(q_rows + 31) // 32}, 1, 1)"
+    traffic, traffic_src = ncu_traffic("depth_select2_kernel", grid)
     line = {
         "metric": "kNN-graph contigs/s", "value": value, "unit": "contigs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -227,7 +259,8 @@ def main_ours(args):
                 "note": "every step re-loads both f64 tables from pinned host memory (rg_knn_load) and returns host lists"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
         "roofline": {"kernel": "depth_select2_kernel", "bound": "fp32", "achieved": ach, "peak": fp32,
-                     "unit": "TFLOP/s", "frac": (ach / fp32) if fp32 else None, "traffic": None,
+                     "unit": "TFLOP/s", "frac": (ach / fp32) if fp32 else None, "traffic": traffic,
+                     "traffic_unit": "bytes per launch (dram read + write)", "traffic_source": traffic_src,
                      "peak_source": "live FFMA micro-benchmark (rosella_b200/csrc/microbench.cu); MEASURED_PEAKS.json has no FP32 CUDA-core entry",
                      "algorithmic_flops_per_launch": r["flops_depth"], "launch_ms": r["depth_sel_ms"]},
         "kernels_ms": {"depth_select": r["depth_sel_ms"], "depth_rescore": r["depth_res_ms"],
