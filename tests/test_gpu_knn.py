@@ -83,30 +83,34 @@ def test_knn_synthetic_3000(ctx, variant):
 
 
 @pytest.mark.parametrize("variant", [gpu.VARIANT_RUST, gpu.VARIANT_FLIGHT])
-@pytest.mark.parametrize("block,chunk", [(256, 1024), (992, 992), (320, 352)])
-def test_depth_symmetric_build(ctx, variant, block, chunk, monkeypatch):
+@pytest.mark.parametrize("block,chunk,k,n,samples", [(256, 1024, 30, 3000, 6), (992, 992, 30, 3000, 6), (320, 352, 30, 3000, 6),
+                                                     (256, 512, 100, 1500, 4), (224, 480, 200, 1100, 3),
+                                                     (256, 512, 30, 1000, 131)])
+def test_depth_symmetric_build(ctx, variant, block, chunk, k, n, samples, monkeypatch):
     """Whole-graph coverage builds evaluate each unordered pair once (knn_depth_sym.cu): the lists must equal the batch
     kernel's bit for bit and pass the oracle checks, including rows in different blocks that share their variances
-    (the equal-variance branch whose sign depends on which row is the query, coverage_calculator.rs:638-647)."""
-    tnf, cov, _ = synth.knn_tables(3000, 6, seed=21, flight=variant == gpu.VARIANT_FLIGHT)
-    cov[2500, 1::2] = cov[100, 1::2]            # equal variances across blocks, different means
-    cov[2501, 1::2] = cov[100, 1::2]
-    cov[101] = cov[2600]                        # duplicate rows across blocks
+    (the equal-variance branch whose sign depends on which row is the query, coverage_calculator.rs:638-647), for
+    K' = 64 / 128 / 256 and for sample counts that are staged in chunks."""
+    tnf, cov, _ = synth.knn_tables(n, samples, seed=21, flight=variant == gpu.VARIANT_FLIGHT)
+    a, b = 100, n - 500
+    cov[b, 1::2] = cov[a, 1::2]                 # equal variances across blocks, different means
+    cov[b + 1, 1::2] = cov[a, 1::2]
+    cov[a + 1] = cov[n - 400]                   # duplicate rows across blocks
     cov[7] = 0.0
-    cov[2999, 1::2] = 0.0
+    cov[n - 1, 1::2] = 0.0
     ctx.knn_load(None, cov, variant)
     monkeypatch.setenv("RG_DEPTH_BUILD", "batch")
-    bi, bd, bnv = ctx.knn_search(gpu.GRAPH_DEPTH, 30)
+    bi, bd, bnv = ctx.knn_search(gpu.GRAPH_DEPTH, k)
     monkeypatch.delenv("RG_DEPTH_BUILD")
     monkeypatch.setenv("RG_SYM_BLOCK", str(block))
     monkeypatch.setenv("RG_SYM_CHUNK", str(chunk))
     launches0 = ctx.timings()["kernel_launches"]
-    si, sd, snv = ctx.knn_search(gpu.GRAPH_DEPTH, 30)
-    nb = -(-3000 // block)
+    si, sd, snv = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    nb = -(-n // block)
     assert ctx.timings()["kernel_launches"] - launches0 >= 3 * nb                     # the block path did run
     assert np.array_equal(si, bi) and np.array_equal(sd, bd) and np.array_equal(snv, bnv)
-    for r0 in (90, 2490, 2990):
-        check_against_oracle(cov, oracle.DEPTH, variant, 30, si[r0:r0 + 10], sd[r0:r0 + 10], q_begin=r0, min_recall=0.995)
+    for r0 in (a - 10, b - 10, n - 10):
+        check_against_oracle(cov, oracle.DEPTH, variant, k, si[r0:r0 + 10], sd[r0:r0 + 10], q_begin=r0, min_recall=0.995)
 
 
 def test_knn_sharded_query_ranges(ctx):
