@@ -65,11 +65,19 @@ __device__ __forceinline__ void flush_record(Smem2 &sm, uint32_t *__restrict__ c
     __syncthreads();
 }
 
+// counter increment: a = byte address of the word that holds this thread's counter, inc = 1 << (8 * byte).  One fire-and-forget shared-memory atomic on the
+// containing word (the four warps of a CTA own the four bytes of a word, and a byte is folded before it can carry)
+// instead of a load / add / store of the byte: one LSU instruction per base and no dependent chain.
+// tb packs both: bits [2,7) = lane (the word of the row), bits [0,2) = warp (the byte of the word).
+__device__ __forceinline__ void bump(uint8_t *__restrict__ cb, uint32_t a, uint32_t inc) {
+    atomicAdd(reinterpret_cast<unsigned int *>(cb + a), inc);
+}
+
 // ---------------------------------------------------------------- packed input (0.375 B/base)
 // One 32-base word: the windows ending at its 32 bases (the first three reach into the previous word).
-// cb = the (CTA-uniform) byte base of the counter plane, tb = lane * 4 + (warp & 3) = this thread's byte in a row
-__device__ __forceinline__ void count_word(uint8_t *__restrict__ cb, uint32_t tb, uint64_t c, uint32_t v, uint32_t pc,
-                                           uint32_t pv) {
+// cb = the (CTA-uniform) byte base of the counter plane, tb = lane * 4 = this lane's word in a row, inc = 1 << 8 warp
+__device__ __forceinline__ void count_word(uint8_t *__restrict__ cb, uint32_t tb, uint32_t inc, uint64_t c, uint32_t v,
+                                           uint32_t pc, uint32_t pv) {
     // 70-bit extended word: bits [0,6) = the previous 3 bases, then the 32 bases of this word
     const uint32_t e0 = ((uint32_t)c << 6) | pc;
     const uint32_t e1 = (uint32_t)(c >> 26);
@@ -86,11 +94,11 @@ __device__ __forceinline__ void count_word(uint8_t *__restrict__ cb, uint32_t tb
     };
     if (vext == 0x7ffffffffull) {               // common case: all 35 bases are A/C/G/T
 #pragma unroll
-        for (int j = 0; j < 32; ++j) cb[addr(j)] += 1;
+        for (int j = 0; j < 32; ++j) bump(cb, addr(j), inc);
     } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            if (((uint32_t)(vext >> j) & 0xfu) == 0xfu) cb[addr(j)] += 1;
+            if (((uint32_t)(vext >> j) & 0xfu) == 0xfu) bump(cb, addr(j), inc);
     }
 }
 
@@ -121,7 +129,7 @@ tnf_count_packed2_kernel(const uint64_t *__restrict__ codes, const uint32_t *__r
     for (int i = tid; i < 256; i += T2) sm.lut[i] = tables[i];
     __syncthreads();
     uint8_t *cb = reinterpret_cast<uint8_t *>(sm.cnt);
-    const uint32_t tb = (tid & 31) * 4 + (tid >> 5);
+    const uint32_t tb = (tid & 31) * 4, inc = 1u << (8 * (tid >> 5));   // word of the row, byte of the word
 
     const uint64_t c_begin = (uint64_t)blockIdx.x * chunks_per_cta;
     const uint64_t c_end = min(c_begin + chunks_per_cta, n_chunks);
@@ -155,7 +163,7 @@ tnf_count_packed2_kernel(const uint64_t *__restrict__ codes, const uint32_t *__r
             const uint64_t c_now = c;
             const uint32_t v_now = v, pc = (uint32_t)(cp >> 58), pv = vp >> 29;
             if (i + 1 < WPT) fetch(w + T2);
-            count_word(cb, tb, c_now, v_now, pc, pv);
+            count_word(cb, tb, inc, c_now, v_now, pc, pv);
         }
         fold_counters(sm, tid);
     }
@@ -171,13 +179,13 @@ struct Roll {
     uint32_t run;     // consecutive A/C/G/T bases seen
 };
 
-__device__ __forceinline__ void count_byte(uint8_t *__restrict__ cb, uint32_t tb, const uint8_t *__restrict__ cls,
-                                           uint32_t byte, Roll &st) {
+__device__ __forceinline__ void count_byte(uint8_t *__restrict__ cb, uint32_t tb, uint32_t inc,
+                                           const uint8_t *__restrict__ cls, uint32_t byte, Roll &st) {
     const uint32_t c = cls[byte];
     if (c == rg::CLS_SKIP) return;              // removed by normalize: the window carries on
     if (c < 4) {
         st.code7 = (st.code7 >> 2) | (c << 13);
-        if (++st.run >= 4) cb[(st.code7 & 0x7f80u) | tb] += 1;
+        if (++st.run >= 4) bump(cb, (st.code7 & 0x7f80u) | tb, inc);
     } else {
         st.run = 0;                             // kept but not a base: breaks the window
     }
@@ -195,7 +203,7 @@ tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restr
     for (int i = tid; i < 256; i += T2) { sm.lut[i] = tables[i]; sm.cls[i] = tables[256 + i]; }
     __syncthreads();
     uint8_t *cb = reinterpret_cast<uint8_t *>(sm.cnt);
-    const uint32_t tb = (tid & 31) * 4 + (tid >> 5);
+    const uint32_t tb = (tid & 31) * 4, inc = 1u << (8 * (tid >> 5));   // word of the row, byte of the word
     const uint8_t *cls = sm.cls;
 
     const uint64_t c_begin = (uint64_t)blockIdx.x * chunks_per_cta;
@@ -244,12 +252,12 @@ tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restr
             const uint32_t wd[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
             if (p0 == base && p1 == base + SEG_BYTES) {
 #pragma unroll
-                for (int b = 0; b < 32; ++b) count_byte(cb, tb, cls, (wd[b >> 2] >> (8 * (b & 3))) & 0xffu, st);
+                for (int b = 0; b < 32; ++b) count_byte(cb, tb, inc, cls, (wd[b >> 2] >> (8 * (b & 3))) & 0xffu, st);
             } else {
                 const int b0 = (int)(p0 - base), b1 = (int)(p1 - base);
 #pragma unroll
                 for (int b = 0; b < 32; ++b)
-                    if (b >= b0 && b < b1) count_byte(cb, tb, cls, (wd[b >> 2] >> (8 * (b & 3))) & 0xffu, st);
+                    if (b >= b0 && b < b1) count_byte(cb, tb, inc, cls, (wd[b >> 2] >> (8 * (b & 3))) & 0xffu, st);
             }
         }
         fold_counters(sm, tid);
