@@ -154,7 +154,7 @@ def test_knn_tnf_euclidean(ctx, golden_dir):
         assert np.all(np.abs(dist[i] - want) <= TAU_REL * np.abs(want) + 1e-12)
 
 
-@pytest.mark.parametrize("k,n", [(1, 300), (48, 400), (100, 700), (200, 600)])
+@pytest.mark.parametrize("k,n", [(1, 300), (48, 400), (50, 2100), (52, 700), (53, 500), (100, 700), (200, 600)])
 def test_knn_k_range(ctx, k, n):
     tnf, cov, _ = synth.knn_tables(n, 3, seed=5 + k)
     (ti, td), (di, dd) = ctx.knn_build(tnf, cov, k)
