@@ -158,10 +158,11 @@ def fp32_peak_tflops():
 
 def workload_config(args, q_rows, world):
     shapes = {(100_000, 10, 30): "configs[1]", (1_000_000, 50, 30): "configs[2]", (5_000_000, 100, 50): "configs[4]"}
-    name = shapes.get((args.n, args.samples, args.k), "not a BASELINE.json shape")
+    name = shapes.get((args.n, args.samples, args.k))
+    name = f"BASELINE.json {name}" if name else "custom shape"
     ref_gb = args.n * (136 + 4 * args.samples) * 4 / 1e9
     return {"workload": f"synthetic {args.n} contigs x (136 TNF + {args.samples} coverage samples), k={args.k}: "
-                        f"exact depth + TNF kNN graphs (BASELINE.json {name})",
+                        f"exact depth + TNF kNN graphs ({name})",
             "n_contigs": args.n, "tnf_bins": 136, "coverage_samples": args.samples, "k": args.k,
             "query_rows_per_gpu_per_step": q_rows, "sharding": f"query rows over {world} rank(s), references replicated",
             "variant": "rust (coverage_calculator.rs:582-666, kmer_counting.rs:366-414)",

@@ -82,3 +82,22 @@ def test_synth_shapes_and_determinism():
     c1, n1, _ = oracle.tnf_count(seq, offs, fast=True)
     c2, n2, _ = oracle.tnf_count(wrapped, woffs, fast=True)
     assert np.array_equal(c1, c2) and np.array_equal(n1, n2)
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` (the oracle port on the host cores) prints one JSON line with the contract's keys;
+    run here at a toy size, the driver runs it at BASELINE.json configs[2]."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--n", "2000", "--samples", "3",
+                          "--k", "10", "--steps", "1", "--warmup", "1", "--cpu-seconds", "1"],
+                         capture_output=True, text=True, timeout=300, check=True).stdout
+    lines = [ln for ln in out.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "contigs/s" and d["value"] > 0 and d["higher_is_better"] is True
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "contigs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["n_contigs"] == 2000 and "workload" in d["config"]
