@@ -38,6 +38,8 @@ def parse_args():
     ap.add_argument("--tnf-gbp", type=float, default=-1.0, help="TNF counting set in Gbp (-1 = auto, 0 = skip)")
     ap.add_argument("--whole-graph-rows", type=int, default=200_000,
                     help="rows of the whole-graph coverage build timed beside the step (N=1 only; 0 = skip)")
+    ap.add_argument("--no-whole-graph-full", action="store_true",
+                    help="skip the one whole build of both graphs at the full shape (SURVEY 8(d) metric; ~55 s on one GPU)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -238,6 +240,36 @@ def whole_graph(ctx, cov, rows, k, rank=0, world=1):
     return out
 
 
+def whole_graph_full(ctx, tnf, cov, k, rank=0, world=1):
+    """SURVEY.md §8(d)'s metric taken literally: N / wall time of the whole build of both graphs at the step's shape,
+    inputs on the host, H2D + transform + kernels + gather (+ D2H of the lists on one GPU) inside the timed region.
+    One untimed-warm-up-free run (the kernels are warm from the steps).  Collective: every rank calls it."""
+    import time
+    import torch
+    from rosella_b200 import dist as rdist, gpu
+    n = tnf.shape[0]
+    if world > 1:       # peer connections of the all-to-all are set up outside the timed region
+        kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
+        rdist.exchange_partial_lists(torch.zeros((n, kp), device="cuda"), torch.zeros((n, kp), dtype=torch.int32, device="cuda"), n, rank, world)
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    if world == 1:
+        ctx.knn_build(tnf, cov, k)                           # rg_knn_build: load + both graphs + host lists
+    else:
+        ctx.knn_load(tnf, cov, gpu.VARIANT_RUST)
+        rdist.build_depth_graph_symmetric(ctx, k, n, rank, world)
+        rdist.build_graph_distributed(ctx, gpu.GRAPH_TNF, k, n, rank, world)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+    return {"workload": f"both graphs of all {n} rows x {cov.shape[1] // 2} samples, k={k}, {world} GPU(s): "
+                        + ("rg_knn_build, host tables in, host lists out" if world == 1 else
+                           "rg_knn_load + symmetric coverage build (all-to-all of partial lists) + TNF row shards, lists gathered on every GPU"),
+            "seconds": float(dt), "contigs_per_s": n / float(dt)}
+
+
 def main_ours(args):
     from benchmarks import cpu_arm, knn_arm, tnf_arm
     helpers = sys.modules[__name__]
@@ -286,6 +318,8 @@ def main_ours(args):
     tnf, cov = r["tables"]
     if r.get("whole_graph"):
         line["whole_graph"] = r["whole_graph"]
+    if r.get("whole_graph_full"):
+        line["whole_graph_full"] = r["whole_graph_full"]
     if world == 1:
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()

@@ -11,14 +11,14 @@ timeout 900 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo 
 timeout 300 python bench.py --impl reference --steps 1 --warmup 1 > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err; echo "ref rc=$?"
 # ncu: launch list of the bench command (values printed under ncu are never bench values)
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_ncu_launches.csv \
-    python bench.py --steps 2 --warmup 1 --no-cpu-baseline --tnf-gbp 1 --whole-graph-rows 40000 > $O/${TAG}_ncu_bench.log 2>&1; echo "ncu list rc=$?"
+    python bench.py --steps 2 --warmup 1 --no-cpu-baseline --tnf-gbp 1 --whole-graph-rows 40000 --no-whole-graph-full > $O/${TAG}_ncu_bench.log 2>&1; echo "ncu list rc=$?"
 # ncu: full set of the two select kernels at the bench shape (first timed step)
 timeout 1200 ncu --set full --clock-control none --import-source on -o $O/${TAG}_full_select -f \
     --kernel-name 'regex:depth_select2' --launch-skip 1 --launch-count 1 \
-    python bench.py --steps 1 --warmup 1 --no-cpu-baseline --tnf-gbp 0 --whole-graph-rows 0 > $O/${TAG}_ncu_full_select.log 2>&1; echo "ncu select rc=$?"
+    python bench.py --steps 1 --warmup 1 --no-cpu-baseline --tnf-gbp 0 --whole-graph-rows 0 --no-whole-graph-full > $O/${TAG}_ncu_full_select.log 2>&1; echo "ncu select rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -o $O/${TAG}_full_tc -f \
     --kernel-name 'regex:tnf_select_tc' --launch-skip 1 --launch-count 1 \
-    python bench.py --steps 1 --warmup 1 --no-cpu-baseline --tnf-gbp 0 --whole-graph-rows 0 > $O/${TAG}_ncu_full_tc.log 2>&1; echo "ncu tc rc=$?"
+    python bench.py --steps 1 --warmup 1 --no-cpu-baseline --tnf-gbp 0 --whole-graph-rows 0 --no-whole-graph-full > $O/${TAG}_ncu_full_tc.log 2>&1; echo "ncu tc rc=$?"
 # ncu: full set of the remaining kernels on the short target (second pass)
 timeout 600 ncu --set full --clock-control none --import-source on -o $O/${TAG}_full_other -f \
     --kernel-name 'regex:rescore|tnf_count|tnf_freq|transform' --launch-skip 8 --launch-count 6 \

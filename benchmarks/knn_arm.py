@@ -126,6 +126,9 @@ def run(args, helpers):
         dist.all_reduce(t_loc, op=dist.ReduceOp.MAX)
     total_ms, e2e_total_ms = float(t_loc[0]), float(t_loc[1])
 
+    wgf = None
+    if not args.no_whole_graph_full:
+        wgf = helpers.whole_graph_full(ctx, tnf, cov, k, rank, world)
     wg = None
     if args.whole_graph_rows > 0:
         wg = helpers.whole_graph(ctx, cov, min(args.whole_graph_rows, n), k, rank, world)
@@ -140,6 +143,6 @@ def run(args, helpers):
         "tnf_res_ms": tnf_res_ms, "flops_depth": flops_depth, "flops_tnf": flops_tnf,
         "h2d_per_step": int(h2d_per_step), "d2h_per_step": int(d2h_per_step), "gen_s": gen_s,
         "load_h2d_ms": load_t["h2d_ms"], "load_transform_ms": load_t["transform_ms"],
-        "tables": (tnf, cov), "ctx": ctx, "whole_graph": wg,
+        "tables": (tnf, cov), "ctx": ctx, "whole_graph": wg, "whole_graph_full": wgf,
     }
     return result
