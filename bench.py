@@ -112,9 +112,10 @@ def peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1647.0, "source": "fallback (B200_PROFILING.md)"}
 
 
-def ncu_traffic(kernel: str, grid: str | None = None):
+def ncu_traffic(kernel: str, grid: str | None = None, min_bytes: float = 0.0):
     """DRAM bytes per launch (read + write) of `kernel` from the newest committed `ncu --set full` summary under
-    profiles/ (benchmarks/ncu_summary.py); `grid` restricts to a launch of that grid size.  -> (bytes, file) or (None, None)"""
+    profiles/ (benchmarks/ncu_summary.py); `grid` restricts to a launch of that grid size, `min_bytes` to a launch
+    that moved at least that much (a capture of a smaller input cannot stand in).  -> (bytes, file) or (None, None)"""
     import glob
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     for path in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_ncu_full_summary.json")), reverse=True):
@@ -137,7 +138,7 @@ def ncu_traffic(kernel: str, grid: str | None = None):
                     if v == v and unit in scale:
                         total += v * scale[unit]
                         ok += 1
-            if ok == 2:
+            if ok == 2 and total >= min_bytes:
                 return total, os.path.basename(path)
     return None, None
 
@@ -333,6 +334,8 @@ def main_ours(args):
             t = tnf_arm.run(r["ctx"], int(gbp * 1e9), args.steps, args.warmup, pk["hbm_gbs"], min(32, os.cpu_count() or 8))
             seq, offs = t.pop("sample")
             t["roofline"]["peak_source"] = pk["source"]
+            t["roofline"]["traffic"], t["roofline"]["traffic_source"] = ncu_traffic(
+                "tnf_count_packed2", min_bytes=0.9 * t["roofline"]["algorithmic_bytes"])
             if not args.no_cpu_baseline:
                 t["cpu_baseline"] = cpu_arm.tnf_sample(seq, offs, args.cpu_seconds)
             line["tnf"] = t
