@@ -286,6 +286,8 @@ def main_ours(args):
     ach = r["flops_depth"] / (r["depth_sel_ms"] * 1e-3) / 1e12
     grid = f"({(q_rows + 31) // 32}, 1, 1)"
     traffic, traffic_src = ncu_traffic("depth_select2_kernel", grid)
+    tc_traffic, tc_traffic_src = ncu_traffic("tnf_select_tc_kernel", f"({(q_rows + 127) // 128}, 1, 1)",
+                                             min_bytes=0.9 * args.n * 136 * 8)     # hi + lo tf32 planes read at least once
     line = {
         "metric": "kNN-graph contigs/s", "value": value, "unit": "contigs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -310,7 +312,8 @@ def main_ours(args):
                                 "achieved": 3.0 * r["flops_tnf"] / (r["tnf_sel_ms"] * 1e-3) / 1e12,
                                 "peak": pk["bf16_tflops"] / 2.0, "unit": "TFLOP/s",
                                 "frac": 3.0 * r["flops_tnf"] / (r["tnf_sel_ms"] * 1e-3) / 1e12 / (pk["bf16_tflops"] / 2.0),
-                                "traffic": None, "peak_source": pk["source"] + ", bf16 / 2 for TF32",
+                                "traffic": tc_traffic, "traffic_source": tc_traffic_src,
+                                "peak_source": pk["source"] + ", bf16 / 2 for TF32",
                                 "algorithmic_flops_per_launch": r["flops_tnf"], "launch_ms": r["tnf_sel_ms"],
                                 "note": "tcgen05.mma kind::tf32, 3 passes for FP32 accuracy; algorithmic = 2*136 flop per pair"},
         "full_build_seconds_est": args.n / value,
