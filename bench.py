@@ -172,6 +172,23 @@ def workload_config(args, q_rows, world):
             "l2": f"256 MB buffer zeroed between timed iterations; reference set ({ref_gb:.1f} GB FP32) exceeds L2"}
 
 
+DEFAULT_QUERY_ROWS = 2 * (2 * 148 * 32)      # two waves of depth-select CTAs on the 148 SMs of a B200
+
+
+def reference_code_c1():
+    """Baseline C1: the reference's own flight distance code, timed single-threaded as the reference
+    drives it.  /root/reference exists in the build container only, so the measurement is the committed
+    profiles/r2_c1_flight_cpu.json (benchmarks/c1_flight_cpu.py), quoted with where it was taken."""
+    p = os.path.join(ROOT, "profiles", "r2_c1_flight_cpu.json")
+    try:
+        d = json.load(open(p))
+        return {"source": "profiles/r2_c1_flight_cpu.json", "where": d.get("where"), "host_cores": d.get("host_cores"),
+                "threads_used": d.get("threads_used"), "n": d.get("n"), "us_per_pair": d.get("runs"),
+                "extrapolation": d.get("extrapolation")}
+    except (OSError, ValueError) as e:
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+
+
 def main_reference(args):
     """--impl reference: the reference's own CPU path for this workload, timed on the host cores.
     The reference (Rust) cannot be built here or on the GPU box, so this is the oracle port."""
@@ -193,9 +210,10 @@ def main_reference(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * last["seconds"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, last["rows"], 1),
+            # the SAME config as the GPU arm (the sample the CPU actually processed is in cpu_baseline.sample)
+            "config": workload_config(args, min(args.query_rows or DEFAULT_QUERY_ROWS, args.n // max(args.gpus, 1)), max(args.gpus, 1)),
             "cpu_baseline": {"value": v, "unit": "contigs/s", "cores": last["cores"], "kind": "port",
-                             "sample": last["sample"]},
+                             "sample": last["sample"], "reference_code": reference_code_c1()},
             "e2e": {"value": v, "unit": "contigs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -215,7 +233,7 @@ def whole_graph(ctx, cov, rows, k, rank=0, world=1):
         kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
         rdist.exchange_partial_lists(torch.zeros((rows, kp), device="cuda"), torch.zeros((rows, kp), dtype=torch.int32, device="cuda"), rows, rank, world)
     for mode in ("batch", "symmetric"):
-        os.environ["RG_DEPTH_BUILD"] = "batch" if mode == "batch" else "sym"
+        ctx.set_option("depth_build", 1 if mode == "batch" else 0)
         torch.cuda.synchronize()
         if world > 1:
             torch.distributed.barrier()
@@ -233,7 +251,7 @@ def whole_graph(ctx, cov, rows, k, rank=0, world=1):
         out[f"{mode}_s"] = float(dt)
         if world == 1:
             out[f"{mode}_select_ms"] = ctx.timings()["select_ms"]
-    os.environ.pop("RG_DEPTH_BUILD", None)
+    ctx.set_option("depth_build", 0)
     same = (np.array_equal if world == 1 else torch.equal)
     out["identical"] = bool(same(res["batch"][0], res["symmetric"][0]) and same(res["batch"][1], res["symmetric"][1]))
     out["contigs_per_s_symmetric"] = rows / out["symmetric_s"]
@@ -328,6 +346,7 @@ def main_ours(args):
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()
                                     if k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"]["reference_code"] = reference_code_c1()
         gbp = args.tnf_gbp
         if gbp < 0:
             import psutil

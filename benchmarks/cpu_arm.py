@@ -12,10 +12,19 @@ import time
 import numpy as np
 
 
+def host_threads() -> int:
+    """Cores this process may run on.  NOT omp_get_max_threads(): torch.distributed.run exports OMP_NUM_THREADS=1 to
+    every rank, which made the round-1 reference arm run on one thread at N > 1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def knn_sample(tnf, cov, k: int, budget_s: float, variant: int = 0, threads: int = 0):
     """Exhaustive exact kNN (both graphs) for a bounded number of query rows against ALL rows."""
     import oracle
-    threads = threads or oracle.max_threads()
+    threads = threads or host_threads()
     n = tnf.shape[0]
     rng = np.random.default_rng(1)
 
@@ -40,7 +49,7 @@ def tnf_sample(seq, offs, budget_s: float, threads: int = 0):
     """Faithful single-thread restatement of KmerCounter::run (what the reference does) and a LUT/OpenMP
     version on all cores, on a prefix of the contig set."""
     import oracle
-    threads = threads or oracle.max_threads()
+    threads = threads or host_threads()
     n = len(offs) - 1
     # prefix of ~64 Mbp for calibration
     cut = int(np.searchsorted(offs, min(int(offs[-1]), 32_000_000)))

@@ -34,7 +34,7 @@ extern "C" {
 #endif
 
 #define RG_NBINS 136u          /* canonical 4-mers, kmer_counting.rs:11,:132-169 */
-#define RG_ABI_VERSION 1
+#define RG_ABI_VERSION 2
 
 typedef struct rg_handle rg_handle;
 
@@ -67,6 +67,14 @@ const char *rg_last_error(const rg_handle *h);
 int32_t rg_sync(rg_handle *h);
 /* the CUDA stream (cudaStream_t) all of the handle's work is issued on */
 void *rg_stream(rg_handle *h);
+/* Behaviour switches live on the handle; the library never reads the process environment.
+ *   "depth_build"      0 automatic (default), 1 batch kernel, 2 symmetric block build for whole-graph searches
+ *   "sym_block"        rows per block of the symmetric build (0 = 9472 = one wave of CTAs)
+ *   "sym_chunk"        columns per evaluation launch of the symmetric build (0 = 4 blocks)
+ *   "tnf_select_impl"  0 automatic (tcgen05 where its shape limits allow), 1 FP32 CUDA-core kernel
+ *   "certify"          1 (default) margin certificate + exhaustive f64 pass for uncertified rows; 0 = off (A/B only)
+ *   "kprime_depth", "kprime_tnf"   candidate-list length override (0 = automatic; 48 (TNF only), 64, 128 or 256) */
+int32_t rg_set_option(rg_handle *h, const char *key, int64_t value);
 
 /* ------------------------------------------------------------------ TNF counting */
 /* the 136 canonical 4-mers in bin order, 4 bytes each, no terminator (host only) */
@@ -175,8 +183,16 @@ typedef struct {
     double tnf_count_ms;     /* last TNF counting kernel (device time) */
     uint64_t kernel_launches; /* kernels launched by this handle since creation */
     uint64_t h2d_bytes, d2h_bytes; /* since creation */
+    /* exactness bookkeeping since the last rg_knn_load (ABI 2) */
+    uint64_t rows_flagged;   /* query rows whose FP32 select margin could not be certified (or sit in a dense collision group) */
+    uint64_t rows_exact;     /* query rows re-evaluated exhaustively in f64 against all n rows */
+    uint64_t extra_pairs;    /* directed (row, candidate) pairs added because an FP32-rounded mean / variance collides */
 } rg_timings;
 int32_t rg_get_timings(rg_handle *h, rg_timings *out);
+/* The rows of the LAST search whose select margin was not certified (they were re-evaluated exhaustively): local row
+ * (bit 31: the row's FP32 operands collide wholesale), the k-th f64 distance among its candidates, its measured select
+ * error.  Any output may be NULL; at most cap entries are written, *count gets the number found.  Synchronises. */
+int32_t rg_knn_flagged_rows(rg_handle *h, uint32_t *rows, float *kth_dist, float *select_eps, uint64_t cap, uint64_t *count);
 
 #ifdef __cplusplus
 }

@@ -6,6 +6,10 @@
                       (flight/flight/metrics.py: metabat_distance_nn :445-538, rho :601-645,
                       tnf_euclidean :64-77, coverage_distance :429-443) on seeded inputs.
                       This is what PINS the oracle's flight variant.
+  rust_pin.npz        the same numba metabat_distance_nn evaluated on (mean - 9e-7, var - 9e-7): where no clamp and
+                      no equal-variance sign rule fires this IS MetabatDistance::distance of
+                      coverage_calculator.rs:588-666 (epsilon 1e-7 instead of 1e-6) — it pins the RUST variant's main
+                      branch on reference-run output (make_rust_pin).
   tnf_fixtures.npz    the reference's bundled FASTA inputs (tests/data/ben/random10000.fna and
                       the first records of 1.fna.gz) as bytes + offsets, with counts produced by
                       a literal pure-Python model of kmer_counting.rs:64-109 written here
@@ -79,6 +83,48 @@ def make_flight(m):
     out["tnf_euclidean"] = eu
     np.savez_compressed(os.path.join(OUT, "flight_metrics.npz"), **out)
     print("flight_metrics.npz:", {k: v.shape for k, v in out.items()})
+
+
+def make_rust_pin(m):
+    """Pin of the RUST variant's main branch on reference-run output.
+
+    MetabatDistance::distance (coverage_calculator.rs:588-666) adds EPSILON = 1e-7 where flight's
+    metabat_distance_nn (metrics.py:445-538) adds 1e-6, so rust(mean, var) and flight(mean - 9e-7, var - 9e-7) are
+    the same function wherever the remaining differences cannot fire:
+      * flight clamps each sample's d to [1e-6, 1 - 1e-6]           -> keep pairs whose per-sample d (the reference
+        function evaluated on the one-sample slices) lies strictly inside;
+      * the equal-variance branch takes abs() in flight, keeps the sign in Rust (:647 vs metrics.py:516-519)
+        -> `noneq` marks pairs in which no contributing sample takes that branch; on the others Rust returns either
+        the same value (all signs positive) or 1.0 (ln of a negative value -> NaN -> 1.0, :659-661);
+      * present means are >= 1e-5, so "mean + eps > eps" agrees (flight sees mean + 1e-7 > 1e-6).
+    statrs' cdf is 0.5 erfc(.), flight's 0.5 (1 + erf(.)): <= 1e-10 relative on d >= 1e-6."""
+    rng = np.random.default_rng(20261105)
+    out = {}
+    SH = 9e-7
+    for s in (1, 3, 10):
+        cov = coverage_rows(rng, 48, s)
+        sh = cov - SH                       # every entry: flight adds 1e-6 to means AND variances
+        n = len(cov)
+        val = np.zeros((n, n)); noclamp = np.zeros((n, n), bool); noneq = np.zeros((n, n), bool)
+        for i in range(n):
+            for j in range(n):
+                val[i, j] = m.metabat_distance_nn(sh[i], sh[j])
+                ok, ne = True, True
+                for t in range(s):
+                    am, bm = sh[i, 2 * t] + 1e-6, sh[j, 2 * t] + 1e-6
+                    if not ((am > 1e-6 or bm > 1e-6) and am != bm):
+                        continue
+                    d1 = m.metabat_distance_nn(sh[i, 2 * t:2 * t + 2], sh[j, 2 * t:2 * t + 2])
+                    ok &= 1e-6 < d1 < 1 - 1e-6
+                    av, bv = max(sh[i, 2 * t + 1] + 1e-6, 1.0), max(sh[j, 2 * t + 1] + 1e-6, 1.0)
+                    ne &= abs(av - bv) >= 1e-4
+                noclamp[i, j], noneq[i, j] = ok, ne
+        out[f"cov_s{s}"] = cov
+        out[f"metabat_rust_mainbranch_s{s}"] = val
+        out[f"noclamp_s{s}"] = noclamp
+        out[f"noneq_s{s}"] = noneq
+    np.savez_compressed(os.path.join(OUT, "rust_pin.npz"), **out)
+    print("rust_pin.npz:", {k: (v.shape, int(v.sum()) if v.dtype == bool else None) for k, v in out.items()})
 
 
 def read_fasta(fh):
@@ -156,4 +202,6 @@ def make_tnf():
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     make_tnf()
-    make_flight(load_flight_metrics())
+    fm = load_flight_metrics()
+    make_flight(fm)
+    make_rust_pin(fm)

@@ -15,19 +15,20 @@ GRAPH_TNF, GRAPH_DEPTH, GRAPH_TNF_EUCLID = 0, 1, 2
 
 # every symbol include/rosella_gpu.h declares (tests check the .so exports exactly these)
 SYMBOLS = [
-    "rg_abi_version", "rg_create", "rg_destroy", "rg_last_error", "rg_sync", "rg_stream",
+    "rg_abi_version", "rg_create", "rg_destroy", "rg_last_error", "rg_sync", "rg_stream", "rg_set_option",
     "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
     "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
-    "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings",
+    "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
 ]
 
 
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("transform_ms", C.c_double), ("select_ms", C.c_double),
                 ("rescore_ms", C.c_double), ("d2h_ms", C.c_double), ("tnf_count_ms", C.c_double),
-                ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("rows_flagged", C.c_uint64), ("rows_exact", C.c_uint64), ("extra_pairs", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -60,6 +61,7 @@ def load() -> C.CDLL:
         "rg_last_error": (C.c_char_p, [vp]),
         "rg_sync": (C.c_int32, [vp]),
         "rg_stream": (vp, [vp]),
+        "rg_set_option": (C.c_int32, [vp, C.c_char_p, C.c_int64]),
         "rg_tnf_canonical_kmers": (C.c_int32, [u8p]),
         "rg_tnf_count_ascii": (C.c_int32, [vp, u8p, u64p, C.c_uint64, u32p, u64p, f64p]),
         "rg_tnf_packed_words": (C.c_uint64, [u8p, u64p, C.c_uint64]),
@@ -82,6 +84,7 @@ def load() -> C.CDLL:
         "rg_graph_mutual": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
+        "rg_knn_flagged_rows": (C.c_int32, [vp, u32p, f32p, f32p, C.c_uint64, C.POINTER(C.c_uint64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -52,7 +52,13 @@ __device__ __forceinline__ void depth_sample2(const pk ax, const pk ay, const pk
     const pk t = fma2(ndv, bc(b.z) - az, D * D);
     const pk q = (ay * bc(b.y)) * t;                                    // :625
     const pk tmp = mk(mufu_sqrt(fabsf(lo(q))), mufu_sqrt(fabsf(hi(q))));
-    const bool eq0 = fabsf(lo(ndv)) < 1e-4f, eq1 = fabsf(hi(ndv)) < 1e-4f; // :620
+    // :620 |a_var - b_var| < MIN_VAR_EPSILON, with the threshold lowered by the rounding error of the FP32 difference
+    // (2^-24 (va + vb) <= 2^-23 vb here; 2^-21 vb is subtracted) so that "equal" in FP32 implies "equal" in f64 — the
+    // branch keeps a sign in the Rust variant (:647), and a sign applied to a pair the reference sends through the
+    // general branch would turn a finite distance into 1.0.  Above vb = 209 only exactly equal FP32 variances pass;
+    // those are f64-equal or patched as extra candidates (knn_exact.cu).
+    const float eq_thr = fmaxf(fmaf(-4.76837158e-7f, b.y, 1e-4f), 1e-30f);
+    const bool eq0 = fabsf(lo(ndv)) < eq_thr, eq1 = fabsf(hi(ndv)) < eq_thr;
     const pk r = mk(eq0 ? 0.f : mufu_rcp(lo(ndv)), eq1 ? 0.f : mufu_rcp(hi(ndv)));
     // equal-variance branch: he = +-D/2 (0 otherwise); RUST folds the sign of p1.cdf - p2.cdf (:638,:647)
     // into it: + when var_a > var_b, - otherwise

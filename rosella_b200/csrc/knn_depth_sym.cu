@@ -17,8 +17,6 @@
 // Order: candidates reach the list of a row in increasing reference index (blocks I' < I deliver their columns while
 // the outer loop is at I', then the row's own pass runs over J = I, I+1, ...), which is the arrival order topk_insert
 // needs for the (distance, index) tie rule.
-#include <cstdlib>
-
 #include "knn_depth_common.cuh"
 
 namespace {
@@ -170,22 +168,19 @@ __global__ void list_init_kernel(float *cand_d, uint32_t *cand_i, uint64_t count
     }
 }
 
-static uint64_t env_rows(const char *name, uint64_t dflt) {
-    if (const char *e = getenv(name)) {
-        const long v = atol(e);
-        if (v > 0) dflt = (uint64_t)v;
-    }
+static uint64_t opt_rows(uint64_t opt, uint64_t dflt) {
+    if (opt > 0) dflt = opt;
     return (dflt + QB - 1) / QB * QB;
 }
 
 // rows per block: 9472 = 296 x 32, one full wave of 148 SMs x 2 CTAs per evaluation launch
 uint32_t block_rows(const rg_handle *h) {
-    return (uint32_t)std::min<uint64_t>(env_rows("RG_SYM_BLOCK", 296ull * QB), h->n_tiles * RG_TILE);
+    return (uint32_t)std::min<uint64_t>(opt_rows(h->opt_sym_block, 296ull * QB), h->n_tiles * RG_TILE);
 }
 
 // columns per evaluation launch (the width of the distance buffers): 4 blocks
 uint32_t chunk_cols(const rg_handle *h, uint32_t B) {
-    return (uint32_t)std::min<uint64_t>(env_rows("RG_SYM_CHUNK", 4ull * B), h->n_tiles * RG_TILE);
+    return (uint32_t)std::min<uint64_t>(opt_rows(h->opt_sym_chunk, 4ull * B), h->n_tiles * RG_TILE);
 }
 
 // Block I = rows [i0, i0 + ni) is evaluated against the columns [i0, n) in chunks: its own square in full (both
@@ -326,11 +321,11 @@ int32_t merge(rg_handle *h, uint32_t n_parts, const float *pd, const uint32_t *p
 }  // namespace
 
 // Whole-graph builds take the symmetric path once there is more than one block of rows (below that it evaluates the
-// same square as the batch kernel); RG_DEPTH_BUILD=batch keeps the batch kernel, RG_SYM_BLOCK / RG_SYM_CHUNK set the
-// block rows and the columns per launch.
+// same square as the batch kernel); rg_set_option "depth_build" = 1 keeps the batch kernel, 2 forces the block build,
+// "sym_block" / "sym_chunk" set the block rows and the columns per launch.
 bool rg_depth_build_sym_wanted(const rg_handle *h) {
-    if (const char *e = getenv("RG_DEPTH_BUILD"))
-        if (e[0] == 'b') return false;
+    if (h->opt_depth_build == 1) return false;
+    if (h->opt_depth_build == 2) return true;
     return h->n > block_rows(h);
 }
 

@@ -8,8 +8,6 @@
 // tensor cores for this term only if shown within tolerance; FP32 CUDA cores are used and the term
 // is <= 4% of the path's flops at the headline shape, see DESIGN.md §4.3.
 // Selection only — knn_rescore.cu recomputes the kept candidates in f64.
-#include <cstdlib>
-
 #include "knn_tnf_common.cuh"
 #include "rg_internal.cuh"
 
@@ -163,29 +161,27 @@ int32_t launch_k(rg_handle *h, uint32_t kprime, uint64_t q_begin, uint64_t q_cou
 }  // namespace
 
 bool rg_tnf_select_tc_supported(const rg_handle *h, uint32_t kprime);
+int32_t rg_ensure_tnf_tiles(rg_handle *h);
 int32_t rg_launch_tnf_select_tc(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count);
 
 // The tcgen05 kernel (knn_tnf_tc.cu) is the product path wherever its shape limits allow (K' = 64, d % 8 == 0);
-// larger K' lists do not fit in registers and take the FP32 CUDA-core kernel below.  RG_TNF_SELECT_IMPL=fp32
-// forces the CUDA-core kernel for A/B measurements.
-static bool force_fp32() {
-    static const bool f = [] { const char *e = getenv("RG_TNF_SELECT_IMPL"); return e && e[0] == 'f'; }();
-    return f;
-}
+// larger K' lists do not fit in registers and take the FP32 CUDA-core kernel below.  rg_set_option(h,
+// "tnf_select_impl", 1) forces the CUDA-core kernel for A/B measurements.
 
 // K' of the TNF graphs: the tensor-core kernel evaluates the dot product to FP32 accuracy (3xTF32), so a margin of
 // 12-16 candidates over k covers the pairs whose FP32 order can differ from the f64 order: k <= 32 takes 48
 // candidates and k <= 52 (BASELINE.json configs[4] has k = 50) takes 64; everything else keeps the general K'
 // (knn_rescore.cu: pick_kprime) and the FP32 CUDA-core kernel
 uint32_t rg_tnf_kprime(const rg_handle *h, uint32_t k, uint32_t general) {
-    if (force_fp32()) return general;
+    if (h->opt_tnf_fp32) return general;
     if (k <= 32 && rg_tnf_select_tc_supported(h, 48)) return 48;
     if (k <= 52 && rg_tnf_select_tc_supported(h, 64)) return 64;
     return general;
 }
 
 int32_t rg_launch_tnf_select(rg_handle *h, uint32_t which, uint32_t kprime, uint64_t q_begin, uint64_t q_count) {
-    if (!force_fp32() && rg_tnf_select_tc_supported(h, kprime)) return rg_launch_tnf_select_tc(h, which, kprime, q_begin, q_count);
+    if (!h->opt_tnf_fp32 && rg_tnf_select_tc_supported(h, kprime)) return rg_launch_tnf_select_tc(h, which, kprime, q_begin, q_count);
+    RG_TRY(rg_ensure_tnf_tiles(h));
     if (which == RG_GRAPH_TNF_EUCLID) return launch_k<METRIC_EUCLID>(h, kprime, q_begin, q_count);
     return h->variant == RG_VARIANT_FLIGHT ? launch_k<RG_VARIANT_FLIGHT>(h, kprime, q_begin, q_count)
                                            : launch_k<RG_VARIANT_RUST>(h, kprime, q_begin, q_count);

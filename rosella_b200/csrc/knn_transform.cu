@@ -53,11 +53,13 @@ __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n,
             if (!isfinite(c)) { bad = 1; c = 0.0; }
             nn += c * c;
             const float cf = (float)c;
-            out[((tile * (d / 4) + j / 4) * RG_TILE + r) * 4 + (j & 3)] = cf;
-            const float h = to_tf32(cf);
-            const uint64_t o = ((panel * (d / 4) + j / 4) * RG_PANEL + pr) * 4 + (j & 3);
-            hi[o] = h;
-            lo[o] = to_tf32(cf - h);
+            if (out) out[((tile * (d / 4) + j / 4) * RG_TILE + r) * 4 + (j & 3)] = cf;
+            if (hi) {
+                const float h = to_tf32(cf);
+                const uint64_t o = ((panel * (d / 4) + j / 4) * RG_PANEL + pr) * 4 + (j & 3);
+                hi[o] = h;
+                lo[o] = to_tf32(cf - h);
+            }
         }
     }
 #pragma unroll
@@ -65,7 +67,7 @@ __global__ void tnf_transform_kernel(const double *__restrict__ tnf, uint64_t n,
     bad = __any_sync(0xffffffffu, bad);
     // a row with a non-finite centred value (ln 0 in the CLR, kmer_counting.rs:351) is stored as zeros
     // with a NaN norm: every distance to it becomes NaN -> 1.0 exactly as :410 does in f64
-    if (lane == 0) {
+    if (lane == 0 && norm) {
         norm[row] = bad ? __int_as_float(0x7fc00000) : (float)nn;
         mean[row] = row < n && isfinite(mu) ? (float)mu : 0.f;
     }
@@ -88,6 +90,7 @@ __global__ void cov_transform_kernel(const double *__restrict__ cov, uint64_t n,
             mean = cov[row * 2 * s + 2 * smp];
             var = cov[row * 2 * s + 2 * smp + 1];
             if (!isfinite(mean) || !isfinite(var)) { atomicOr(err_flag, 1u); mean = 0.0; var = 0.0; }
+            if (mean < 0.0) { atomicOr(err_flag, 2u); mean = 0.0; }
         }
         const double m = mean + eps;
         double v = var + eps;
@@ -96,6 +99,23 @@ __global__ void cov_transform_kernel(const double *__restrict__ cov, uint64_t n,
         const bool present = m > eps;
         out[t] = make_float4((float)m, (float)v, (float)log(v), (float)(present ? inv : -inv));
     }
+}
+
+int32_t rg_build_collision_patches(rg_handle *h, uint64_t n, uint32_t s, uint32_t variant);
+
+// tnf_t (FP32 centred rows, tile-major) is read only by the FP32 CUDA-core TNF select (K' > 64, d % 8 != 0 or forced):
+// built on first use so that the tensor-core path does not keep 0.5 GB per million rows for nothing
+int32_t rg_ensure_tnf_tiles(rg_handle *h) {
+    if (h->tnf_t_valid) return RG_OK;
+    const uint64_t rows_padded = h->n_panels * RG_PANEL;
+    RG_TRY(rg_reserve(h, h->tnf_t, rows_padded * h->d * sizeof(float)));
+    const int wpb = 8;
+    tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
+        (const double *)h->tnf64.p, h->n, h->d, (float *)h->tnf_t.p, nullptr, nullptr, nullptr, nullptr);
+    RG_CUDA(h, cudaGetLastError());
+    h->tm.kernel_launches += 1;
+    h->tnf_t_valid = true;
+    return RG_OK;
 }
 
 extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
@@ -120,7 +140,6 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
     if (tnf) {
         RG_TRY(rg_reserve(h, h->tnf64, n * d * sizeof(double)));
-        RG_TRY(rg_reserve(h, h->tnf_t, rows_padded * d * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_norm, rows_padded * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_mean, rows_padded * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_hi, rows_padded * d * sizeof(float)));
@@ -138,7 +157,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     if (tnf) {
         const int wpb = 8;
         tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
-            (const double *)h->tnf64.p, n, d, (float *)h->tnf_t.p, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p,
+            (const double *)h->tnf64.p, n, d, nullptr, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p,
             (float *)h->tnf_hi.p, (float *)h->tnf_lo.p);
         RG_CUDA(h, cudaGetLastError());
         h->tm.kernel_launches += 1;
@@ -159,10 +178,25 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     RG_CUDA(h, cudaStreamSynchronize(h->stream));
     h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.transform_ms = rg_elapsed(h->ev[1], h->ev[2]);
-    if (flag)
+    if (flag & 1u)
         return rg_fail(h, RG_ERR_INVALID,
                        "rg_knn_load: coverage table holds a non-finite value (the reference panics in "
                        "Normal::new, coverage_calculator.rs:639)");
+    if (flag & 2u)
+        return rg_fail(h, RG_ERR_INVALID,
+                       "rg_knn_load: coverage table holds a negative mean (coverage is a read depth; the select phase "
+                       "relies on mean + eps >= eps for coverage_calculator.rs:619)");
+    h->has_extra = false;
+    h->n_extra = 0;
+    h->tnf_t_valid = false;
+    if (h->cert_ctr.p) RG_CUDA(h, cudaMemsetAsync(h->cert_ctr.p, 0, 8 * sizeof(uint32_t), h->stream));
+    if (cov && h->opt_certify) {
+        RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+        RG_TRY(rg_build_collision_patches(h, n, s, variant));
+        RG_CUDA(h, cudaEventRecord(h->ev[2], h->stream));
+        RG_CUDA(h, cudaEventSynchronize(h->ev[2]));
+        h->tm.transform_ms += rg_elapsed(h->ev[1], h->ev[2]);
+    }
     h->n = n; h->d = d; h->s = s; h->variant = variant; h->n_tiles = n_tiles; h->n_panels = n_panels;
     h->has_tnf = tnf != nullptr;
     h->has_cov = cov != nullptr;

@@ -55,7 +55,10 @@ __global__ void k_mufu(float *out) {
 #pragma unroll
         for (int c = 0; c < CHAINS; ++c) {
             if (OP == 0) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[c]));
-            if (OP == 1) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(x[c]));
+            if (OP == 1) {   // rcp(rcp(x)) = x lets ptxas fold the chain away: break the identity with one FFMA (FMA pipe, not XU)
+                asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(x[c]));
+                x[c] = fmaf(x[c], 1.0000001f, 1e-9f);
+            }
             if (OP == 2) asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(x[c]));
             if (OP == 3) asm volatile("sqrt.approx.ftz.f32 %0, %0;" : "+f"(x[c]));
         }

@@ -83,7 +83,8 @@ void rg_destroy(rg_handle *h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevBuf *bufs[] = {&h->tnf64, &h->cov64, &h->tnf_t, &h->tnf_norm, &h->tnf_mean, &h->tnf_hi, &h->tnf_lo, &h->cov_t, &h->err_flag,
-                      &h->cand_d, &h->cand_i, &h->sym_d, &h->sym_t, &h->out_i, &h->out_d, &h->out_nv, &h->codes, &h->valid,
+                      &h->cand_d, &h->cand_i, &h->sym_d, &h->sym_t, &h->out_i, &h->out_d, &h->out_nv, &h->flag_list, &h->cert_ctr, &h->exact_scratch,
+                      &h->row_flag, &h->extra_off, &h->extra_idx, &h->codes, &h->valid,
                       &h->woff, &h->ascii, &h->aoff, &h->counts, &h->nkmers, &h->freqs, &h->tnf_tables,
                       &h->chunk_start};
     for (DevBuf *b : bufs) rg_release(*b);
@@ -108,6 +109,22 @@ int32_t rg_sync(rg_handle *h) {
 
 void *rg_stream(rg_handle *h) { return h ? (void *)h->stream : nullptr; }
 
+int32_t rg_set_option(rg_handle *h, const char *key, int64_t value) {
+    if (!h) return RG_ERR_INVALID;
+    if (!key) return rg_fail(h, RG_ERR_INVALID, "rg_set_option: key is NULL");
+    const std::string k(key);
+    auto bad = [&]() { return rg_fail(h, RG_ERR_INVALID, "rg_set_option: value %lld is not valid for \"%s\"", (long long)value, key); };
+    if (k == "depth_build") { if (value < 0 || value > 2) return bad(); h->opt_depth_build = (int)value; }
+    else if (k == "sym_block") { if (value < 0) return bad(); h->opt_sym_block = (uint64_t)value; }
+    else if (k == "sym_chunk") { if (value < 0) return bad(); h->opt_sym_chunk = (uint64_t)value; }
+    else if (k == "tnf_select_impl") { if (value < 0 || value > 1) return bad(); h->opt_tnf_fp32 = (int)value; }
+    else if (k == "certify") { if (value < 0 || value > 1) return bad(); h->opt_certify = (int)value; }
+    else if (k == "kprime_depth") { if (value != 0 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_depth = (uint32_t)value; }
+    else if (k == "kprime_tnf") { if (value != 0 && value != 48 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_tnf = (uint32_t)value; }
+    else return rg_fail(h, RG_ERR_INVALID, "rg_set_option: unknown key \"%s\"", key);
+    return RG_OK;
+}
+
 int32_t rg_get_timings(rg_handle *h, rg_timings *out) {
     if (!h || !out) return RG_ERR_INVALID;
     if (h->tm.select_ms < 0.0) {   // asynchronous search pending: events 3..5 bracket select / rescore
@@ -121,6 +138,15 @@ int32_t rg_get_timings(rg_handle *h, rg_timings *out) {
         RG_CUDA(h, cudaEventSynchronize(h->ev[7]));
         h->tm.tnf_count_ms = rg_elapsed(h->ev[6], h->ev[7]);
     }
+    if (h->cert_ctr.p) {
+        uint32_t c[4] = {};
+        RG_CUDA(h, cudaSetDevice(h->device));
+        RG_CUDA(h, cudaMemcpyAsync(c, h->cert_ctr.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+        RG_CUDA(h, cudaStreamSynchronize(h->stream));
+        h->tm.rows_flagged = c[1];
+        h->tm.rows_exact = c[2];
+    }
+    h->tm.extra_pairs = h->n_extra;
     *out = h->tm;
     return RG_OK;
 }

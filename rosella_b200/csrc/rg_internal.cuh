@@ -32,7 +32,8 @@ struct rg_handle {
     uint64_t n_tiles = 0;
     bool has_tnf = false, has_cov = false;
     DevBuf tnf64, cov64;      // the caller's f64 tables, kept for the f64 re-evaluation
-    DevBuf tnf_t;             // f32 centred rows, tile-major [tile][d/4][32] float4
+    DevBuf tnf_t;             // f32 centred rows, tile-major [tile][d/4][32] float4 (built on demand: rg_ensure_tnf_tiles)
+    bool tnf_t_valid = false;
     DevBuf tnf_norm;          // f32 [n_tiles*32] sum of squares of the centred row (NaN = non-finite row)
     DevBuf tnf_mean;          // f32 [n_tiles*32] mean of the row as passed (Euclidean graph)
     DevBuf tnf_hi, tnf_lo;    // tf32 split of the centred rows, panel-major [panels][d/4][128] float4 (tensor-core select)
@@ -44,6 +45,25 @@ struct rg_handle {
     cudaStream_t sym_stream[3] = {};   // two alternating evaluation streams + the reducer stream
     cudaEvent_t sym_ev[5] = {};        // evaluated[2], reduced[2], fork
     DevBuf out_i, out_d, out_nv; // device staging of final lists for host-output calls
+
+    // ---- exactness (knn_exact.cu, knn_rescore.cu)
+    uint64_t flag_rows = 0;   // rows of the last search (flag_list holds 3 arrays of that length)
+    DevBuf flag_list;         // u32 [rows of the search]: local rows whose select margin was not certified
+    DevBuf exact_scratch;     // partial lists + arrival counters of flagged rows that are split over several CTAs
+    DevBuf cert_ctr;          // u32 [8]: [0] rows in flag_list (reset per search), [1] rows flagged since the load,
+                              //          [2] rows re-evaluated exhaustively in f64 since the load
+    DevBuf row_flag;          // u8 [n]: 1 = this row always takes the exhaustive f64 pass (dense FP32 collision group)
+    DevBuf extra_off;         // u64 [n+1] CSR of the extra candidates of each row ...
+    DevBuf extra_idx;         // u32 [...]: rows whose FP32 mean / variance collides with the row's while the f64 values differ
+    uint64_t n_extra = 0;     // directed extra candidate pairs found by the last load
+    bool has_extra = false;
+
+    // ---- options (rg_set_option); the library never reads the environment
+    int opt_depth_build = 0;          // 0 = automatic, 1 = batch kernel, 2 = symmetric block build
+    uint64_t opt_sym_block = 0, opt_sym_chunk = 0;   // rows per block / columns per launch of the symmetric build (0 = default)
+    int opt_tnf_fp32 = 0;             // 1 = force the FP32 CUDA-core TNF select
+    int opt_certify = 1;              // 0 = skip the margin certificate and the exhaustive pass (A/B measurements only)
+    uint32_t opt_kprime_depth = 0, opt_kprime_tnf = 0;   // candidate-list override (test hook; 0 = automatic)
 
     // ---- TNF counting state
     uint64_t tnf_n = 0, tnf_words = 0, tnf_bytes = 0;

@@ -64,6 +64,10 @@ class Context:
         if rc:
             raise RosellaGpuError(rc, (self.lib.rg_last_error(self.h) or b"").decode())
 
+    def set_option(self, key: str, value: int):
+        """rg_set_option: depth_build, sym_block, sym_chunk, tnf_select_impl, certify, kprime_depth, kprime_tnf."""
+        self._chk(self.lib.rg_set_option(self.h, key.encode(), int(value)))
+
     def sync(self):
         self._chk(self.lib.rg_sync(self.h))
 
@@ -188,6 +192,15 @@ class Context:
                                         _lib.ptr(di, C.c_uint32), _lib.ptr(dd, C.c_float)))
         self._n = n
         return (ti, td), (di, dd)
+
+    def knn_flagged_rows(self, cap: int = 1 << 20):
+        """Rows of the last search that went through the exhaustive pass -> (rows, forced, kth_dist, select_eps)."""
+        rows, dk, eps = np.zeros(cap, np.uint32), np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+        cnt = C.c_uint64(0)
+        self._chk(self.lib.rg_knn_flagged_rows(self.h, _lib.ptr(rows, C.c_uint32), _lib.ptr(dk, C.c_float),
+                                               _lib.ptr(eps, C.c_float), cap, C.byref(cnt)))
+        m = min(cnt.value, cap)
+        return rows[:m] & 0x7FFFFFFF, (rows[:m] >> 31).astype(bool), dk[:m], eps[:m]
 
     # ------------------------------------------------------------------ graph post-ops
     def graph_mutual(self, idx, keep_n_edges: int):

@@ -117,7 +117,7 @@ def test_gloo_world2_partial_list_exchange(tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("variant", [0, 1])
-def test_partial_build_and_merge_on_one_gpu(ctx, variant, monkeypatch):
+def test_partial_build_and_merge_on_one_gpu(ctx, variant):
     """rg_knn_depth_partial_dev for parts 0..2 of 3 run one after the other on one GPU, stacked the way the all-to-all
     delivers them, merged by rg_knn_depth_merge_dev: the lists equal rg_knn_search's bit for bit."""
     import torch
@@ -127,11 +127,11 @@ def test_partial_build_and_merge_on_one_gpu(ctx, variant, monkeypatch):
     cov[2000, 1::2] = cov[17, 1::2]
     cov[1999] = cov[18]
     ctx.knn_load(None, cov, variant)
-    monkeypatch.setenv("RG_DEPTH_BUILD", "batch")
+    ctx.set_option("depth_build", 1)
     i1, d1, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
-    monkeypatch.delenv("RG_DEPTH_BUILD")
-    monkeypatch.setenv("RG_SYM_BLOCK", "224")
-    monkeypatch.setenv("RG_SYM_CHUNK", "512")
+    ctx.set_option("depth_build", 0)
+    ctx.set_option("sym_block", 224)
+    ctx.set_option("sym_chunk", 512)
     kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
     assert kp >= k
     dev = torch.device("cuda", ctx.device)
@@ -152,6 +152,8 @@ def test_partial_build_and_merge_on_one_gpu(ctx, variant, monkeypatch):
         ctx.sync()
         assert np.array_equal(idx.cpu().numpy().astype(np.uint32), i1[qb:qe]) and np.array_equal(dst.cpu().numpy(), d1[qb:qe])
     i2, d2 = rdist.build_depth_graph_symmetric(ctx, k, n, 0, 1)          # world size 1 through the same host code
+    ctx.set_option("sym_block", 0)
+    ctx.set_option("sym_chunk", 0)
     assert np.array_equal(i2.cpu().numpy().astype(np.uint32), i1) and np.array_equal(d2.cpu().numpy(), d1)
 
 

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     lib = _lib.load()
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.rg_abi_version() == 1
+    assert lib.rg_abi_version() == 2
 
 
 def test_canonical_kmers_match_oracle():
@@ -101,3 +101,25 @@ def test_bench_reference_arm_contract():
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": "contigs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["config"]["n_contigs"] == 2000 and "workload" in d["config"]
+
+
+def test_reference_arm_ignores_omp_num_threads_and_mirrors_the_gpu_config():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the reference arm must still use all host cores
+    (round 1 measured one thread at N > 1), and its `config` must be the GPU arm's."""
+    import json
+    import subprocess
+    import sys
+    import bench
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, OMP_NUM_THREADS="1", RANK="0", WORLD_SIZE="4")
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "4", "--n", "40000",
+                          "--samples", "3", "--k", "10", "--steps", "1", "--warmup", "0", "--cpu-seconds", "1"],
+                         capture_output=True, text=True, timeout=300, check=True, env=env).stdout
+    d = json.loads([ln for ln in out.splitlines() if ln.startswith("{")][0])
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert f"OpenMP {d['cpu_baseline']['cores']} threads" in d["cpu_baseline"]["sample"]
+
+    class A:
+        n, samples, k, gpus, query_rows = 40000, 3, 10, 4, 0
+    assert d["config"] == bench.workload_config(A, min(bench.DEFAULT_QUERY_ROWS, A.n // 4), 4)
+    assert "reference_code" in d["cpu_baseline"]

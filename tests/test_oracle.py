@@ -143,3 +143,21 @@ def test_build_mutual_kgraph_restatement_matches_list_semantics():
         assert nbr.tolist() == [e[0] for m in mutual for e in m]
         assert np.array_equal(w, np.array([e[1] for m in mutual for e in m], np.float32))
         assert disc.tolist() == [i for i, m in enumerate(mutual) if not m]
+
+
+@pytest.mark.parametrize("s", [1, 3, 10])
+def test_metabat_rust_variant_main_branch_is_pinned(golden_dir, s):
+    """MetabatDistance::distance (coverage_calculator.rs:588-666) against the reference's own numba
+    metabat_distance_nn run on (mean - 9e-7, var - 9e-7) — where neither flight's clamp nor the equal-variance sign
+    rule can fire the two are the same function (oracle/make_golden.py: make_rust_pin)."""
+    g = np.load(os.path.join(golden_dir, "rust_pin.npz"))
+    cov, ref = g[f"cov_s{s}"], g[f"metabat_rust_mainbranch_s{s}"]
+    noclamp, noneq = g[f"noclamp_s{s}"], g[f"noneq_s{s}"]
+    got = np.array([[oracle.metabat(a, b, oracle.RUST) for b in cov] for a in cov])
+    main = noclamp & noneq
+    assert main.sum() > 800
+    assert np.allclose(got[main], ref[main], rtol=1e-9, atol=0)
+    # pairs with an equal-variance sample: flight takes abs(), Rust keeps the sign -> the same value or NaN -> 1.0
+    eq = noclamp & ~noneq
+    same = np.isclose(got[eq], ref[eq], rtol=1e-9, atol=0)
+    assert (same | (got[eq] == 1.0)).all() and same.any() and (~same).any()
