@@ -219,74 +219,129 @@ def main_reference(args):
 
 
 def whole_graph(ctx, cov, rows, k, rank=0, world=1):
-    """The drop-in call is a build of ALL rows (rg_knn_build): the coverage graph then takes the symmetric block path
-    (knn_depth_sym.cu, every unordered pair once; on N GPUs block shares + all-to-all of partial lists).
-    Timed here on the first `rows` rows of the step's table, beside the batch kernel / query-row shards on the same
-    rows, with the lists compared bit for bit.  Collective: every rank calls it."""
-    import time
+    """The drop-in call is a build of ALL rows: the coverage graph then takes the symmetric block path
+    (knn_depth_sym.cu, every unordered pair once; on N GPUs block shares + all-to-all of partial lists inside the
+    library, knn_dist.cu).  Timed here on the first `rows` rows of the step's table, beside the batch kernel /
+    query-row shards on the same rows, with the lists compared bit for bit.  Collective: every rank calls it."""
     import torch
-    from rosella_b200 import dist as rdist, gpu
-    ctx.knn_load(None, cov[:rows], gpu.VARIANT_RUST)
-    out = {"workload": f"coverage graph of all {rows} rows x {cov.shape[1] // 2} samples, k={k}, {world} GPU(s)"}
+    from rosella_b200 import gpu
+    s = cov.shape[1] // 2
+    ctx.knn_load_dist(None, cov[:rows] if rank == 0 else None, rows, 136, s, gpu.VARIANT_RUST, 0)
+    out = {"workload": f"coverage graph of all {rows} rows x {s} samples, k={k}, {world} GPU(s)"}
     res = {}
-    if world > 1:       # peer connections of the all-to-all are set up outside the timed region
-        kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
-        rdist.exchange_partial_lists(torch.zeros((rows, kp), device="cuda"), torch.zeros((rows, kp), dtype=torch.int32, device="cuda"), rows, rank, world)
+    idx = np.zeros((rows, k), np.uint32)
+    dst = np.zeros((rows, k), np.float32)
     for mode in ("batch", "symmetric"):
         ctx.set_option("depth_build", 1 if mode == "batch" else 0)
         torch.cuda.synchronize()
         if world > 1:
             torch.distributed.barrier()
         t0 = time.perf_counter()
-        if world == 1:
-            res[mode] = ctx.knn_search(gpu.GRAPH_DEPTH, k)[:2]       # host lists returned
-        elif mode == "batch":
-            res[mode] = rdist.build_graph_distributed(ctx, gpu.GRAPH_DEPTH, k, rows, rank, world)
-        else:
-            res[mode] = rdist.build_depth_graph_symmetric(ctx, k, rows, rank, world)
-        torch.cuda.synchronize()
+        ctx.knn_build_dist(gpu.GRAPH_DEPTH, k, gather=True, out=(idx, dst))
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:
             torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
         out[f"{mode}_s"] = float(dt)
+        res[mode] = (idx.copy(), dst.copy())
         if world == 1:
             out[f"{mode}_select_ms"] = ctx.timings()["select_ms"]
     ctx.set_option("depth_build", 0)
-    same = (np.array_equal if world == 1 else torch.equal)
-    out["identical"] = bool(same(res["batch"][0], res["symmetric"][0]) and same(res["batch"][1], res["symmetric"][1]))
+    out["identical"] = bool(np.array_equal(res["batch"][0], res["symmetric"][0]) and np.array_equal(res["batch"][1], res["symmetric"][1]))
     out["contigs_per_s_symmetric"] = rows / out["symmetric_s"]
     out["contigs_per_s_batch"] = rows / out["batch_s"]
     return out
 
 
-def whole_graph_full(ctx, tnf, cov, k, rank=0, world=1):
-    """SURVEY.md §8(d)'s metric taken literally: N / wall time of the whole build of both graphs at the step's shape,
-    inputs on the host, H2D + transform + kernels + gather (+ D2H of the lists on one GPU) inside the timed region.
-    One untimed-warm-up-free run (the kernels are warm from the steps).  Collective: every rank calls it."""
-    import time
-    import torch
-    from rosella_b200 import dist as rdist, gpu
+def parity_sample(ctx, tnf, cov, k, lists, oracle_rows=64, bit_rows=4096, seed=3):
+    """Parity attached to a timed whole-graph build (rank 0, after the clock stopped): `oracle_rows` random rows of both
+    graphs against the exhaustive f64 oracle on the host cores (tie-aware recall must be 1.0; a position may differ only
+    where two neighbours tie within 2 f32 ulps), and `bit_rows` contiguous rows bit-compared with rg_knn_search through
+    the batch kernel (a different select path: no symmetry, no exchange)."""
+    import oracle
+    from rosella_b200 import gpu
     n = tnf.shape[0]
-    if world > 1:       # peer connections of the all-to-all are set up outside the timed region
-        kp = ctx.knn_kprime(gpu.GRAPH_DEPTH, k)
-        rdist.exchange_partial_lists(torch.zeros((n, kp), device="cuda"), torch.zeros((n, kp), dtype=torch.int32, device="cuda"), n, rank, world)
-        torch.cuda.synchronize()
+    rng = np.random.default_rng(seed)
+    rows = np.sort(rng.choice(n, min(oracle_rows, n), replace=False)).astype(np.uint64)
+    out = {"oracle_rows": int(len(rows)), "bit_rows": 0, "graphs": {}}
+    qb = int(rng.integers(0, max(1, n - bit_rows)))
+    qe = min(n, qb + bit_rows)
+    out["bit_rows"] = qe - qb
+    t0 = time.perf_counter()
+    ok = True
+    for name, which, ow, data in (("depth", gpu.GRAPH_DEPTH, oracle.DEPTH, cov), ("tnf", gpu.GRAPH_TNF, oracle.TNF, tnf)):
+        idx, dst = lists[name]
+        oi, od, _ = oracle.knn(data, ow, k, oracle.RUST, qrows=rows)
+        gi, gd = idx[rows], dst[rows]
+        hits = total = 0
+        max_rel = 0.0
+        for r in range(len(rows)):
+            kth = od[r, -1]
+            got = set(gi[r].tolist())
+            for p in range(k):
+                total += 1
+                hits += (int(oi[r, p]) in got) or (od[r, p] >= kth * (1 - 2.4e-7))
+            m = gi[r] == oi[r]
+            if m.any():
+                max_rel = max(max_rel, float(np.max(np.abs(gd[r][m] - od[r][m]) / np.maximum(od[r][m], 1e-30))))
+        ctx.set_option("depth_build", 1)
+        bi, bd, _ = ctx.knn_search(which, k, qb, qe)
+        ctx.set_option("depth_build", 0)
+        bit = bool(np.array_equal(bi, idx[qb:qe]) and np.array_equal(bd, dst[qb:qe]))
+        g = {"recall": hits / max(total, 1), "positions_equal": float((gi == oi).mean()), "max_rel_dist_err": max_rel,
+             "bit_identical_to_batch_kernel": bit}
+        ok &= g["recall"] == 1.0 and bit and max_rel <= 2.4e-7
+        out["graphs"][name] = g
+    out["ok"] = bool(ok)
+    out["seconds"] = time.perf_counter() - t0
+    out["recall"] = min(g["recall"] for g in out["graphs"].values())
+    return out
+
+
+def whole_graph_full(ctx, tnf, cov, k, rank=0, world=1, parity=True):
+    """SURVEY.md §8(d)'s metric taken literally: N / wall time of the whole build of both graphs at the step's shape,
+    inputs on the host (rank 0), H2D + NVLink broadcast + transform + kernels + exchange + complete host lists on every
+    rank inside the timed region.  One pass (the kernels are warm from the steps).  Collective: every rank calls it.
+    Phases are CUDA-event times on the library's stream, max over ranks; `parity_sample` is checked afterwards."""
+    import torch
+    from rosella_b200 import gpu
+    n, s = tnf.shape[0], cov.shape[1] // 2
+    lists = {name: (np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)) for name in ("depth", "tnf")}
+    for a, b in lists.values():
+        a.fill(0); b.fill(0)                                 # touch the pages outside the timed region
+    torch.cuda.synchronize()
+    if world > 1:
         torch.distributed.barrier()
     t0 = time.perf_counter()
-    if world == 1:
-        ctx.knn_build(tnf, cov, k)                           # rg_knn_build: load + both graphs + host lists
-    else:
-        ctx.knn_load(tnf, cov, gpu.VARIANT_RUST)
-        rdist.build_depth_graph_symmetric(ctx, k, n, rank, world)
-        rdist.build_graph_distributed(ctx, gpu.GRAPH_TNF, k, n, rank, world)
-    torch.cuda.synchronize()
-    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    ctx.knn_load_dist(tnf if rank == 0 else None, cov if rank == 0 else None, n, 136, s, gpu.VARIANT_RUST, 0)
+    t_load = time.perf_counter() - t0
+    ctx.knn_build_dist(gpu.GRAPH_DEPTH, k, gather=True, out=lists["depth"])
+    ph_depth = ctx.dist_timings()
+    t_depth = time.perf_counter() - t0 - t_load
+    ctx.knn_build_dist(gpu.GRAPH_TNF, k, gather=True, out=lists["tnf"])
+    ph_tnf = ctx.dist_timings()
+    wall = time.perf_counter() - t0
+    tm = ctx.timings()
+    loc = [wall, t_load, t_depth, wall - t_load - t_depth, ph_depth["load_h2d_ms"], ph_depth["load_bcast_ms"],
+           ph_depth["load_transform_ms"], ph_depth["partial_ms"], ph_depth["exchange_ms"], ph_depth["finish_ms"],
+           ph_depth["gather_ms"], ph_tnf["finish_ms"], ph_tnf["gather_ms"]]
+    t = torch.tensor(loc, dtype=torch.float64, device="cuda")
     if world > 1:
-        torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
-    return {"workload": f"both graphs of all {n} rows x {cov.shape[1] // 2} samples, k={k}, {world} GPU(s): "
-                        + ("rg_knn_build, host tables in, host lists out" if world == 1 else
-                           "rg_knn_load + symmetric coverage build (all-to-all of partial lists) + TNF row shards, lists gathered on every GPU"),
-            "seconds": float(dt), "contigs_per_s": n / float(dt)}
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    v = [float(x) for x in t]
+    out = {"workload": f"both graphs of all {n} rows x {s} samples, k={k}, {world} GPU(s): rg_knn_load_dist + rg_knn_build_dist "
+                       "(host tables on rank 0 in, complete host lists on every rank out)",
+           "seconds": v[0], "contigs_per_s": n / v[0],
+           "phases": {"unit": "ms, max over ranks; CUDA events on the library stream except *_wall_s",
+                      "load_wall_s": v[1], "depth_wall_s": v[2], "tnf_wall_s": v[3],
+                      "load_h2d": v[4], "load_broadcast": v[5], "load_transform_and_collision_scan": v[6],
+                      "depth_partial": v[7], "depth_all_to_all": v[8], "depth_merge_rescore": v[9],
+                      "depth_gather_d2h": v[10], "tnf_select_rescore": v[11], "tnf_gather_d2h": v[12]},
+           "rows_flagged": tm["rows_flagged"], "rows_exact": tm["rows_exact"], "extra_pairs": tm["extra_pairs"]}
+    if parity and rank == 0:
+        out["parity_sample"] = parity_sample(ctx, tnf, cov, k, lists)
+    if world > 1:
+        torch.distributed.barrier()
+    return out
 
 
 def main_ours(args):
@@ -342,6 +397,8 @@ def main_ours(args):
         line["whole_graph"] = r["whole_graph"]
     if r.get("whole_graph_full"):
         line["whole_graph_full"] = r["whole_graph_full"]
+    if r.get("tnf_sharded"):
+        line["tnf"] = r["tnf_sharded"]
     if world == 1:
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = {k: v for k, v in cpu_arm.knn_sample(tnf, cov, args.k, args.cpu_seconds).items()

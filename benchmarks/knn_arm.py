@@ -21,6 +21,9 @@ def run(args, helpers):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n, s, k = args.n, args.samples, args.k
     ctx = gpu.Context(local_rank)
+    if world > 1:
+        from rosella_b200 import dist as rdist
+        rdist.init_comm(ctx, rank, world)           # NCCL communicator inside librosella_gpu.so (rg_comm_init)
     sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
     # depth select: 32 query rows per CTA, 2 CTAs per SM -> a multiple of 2*SMs*32 fills whole waves
     q_rows = args.query_rows or 2 * (2 * sms * 32)
@@ -133,6 +136,12 @@ def run(args, helpers):
     if args.whole_graph_rows > 0:
         wg = helpers.whole_graph(ctx, cov, min(args.whole_graph_rows, n), k, rank, world)
 
+    tnf_sharded = None
+    if world > 1 and args.tnf_gbp != 0:
+        from benchmarks import tnf_arm
+        gbp = args.tnf_gbp if args.tnf_gbp > 0 else 8.0
+        tnf_sharded = tnf_arm.run_sharded(ctx, int(gbp * 1e9), args.steps, rank, world, max(2, min(8, (os.cpu_count() or 8) // world)))
+
     absent_all = (cov[:, 0::2] <= 0).sum(axis=0).astype(np.float64)
     flops_depth = helpers.algorithmic_flops(cov[qb:qe], absent_all, n, graphs_tnf=0)
     flops_tnf = float(q_rows) * n * 272.0
@@ -143,6 +152,6 @@ def run(args, helpers):
         "tnf_res_ms": tnf_res_ms, "flops_depth": flops_depth, "flops_tnf": flops_tnf,
         "h2d_per_step": int(h2d_per_step), "d2h_per_step": int(d2h_per_step), "gen_s": gen_s,
         "load_h2d_ms": load_t["h2d_ms"], "load_transform_ms": load_t["transform_ms"],
-        "tables": (tnf, cov), "ctx": ctx, "whole_graph": wg, "whole_graph_full": wgf,
+        "tables": (tnf, cov), "ctx": ctx, "whole_graph": wg, "whole_graph_full": wgf, "tnf_sharded": tnf_sharded,
     }
     return result

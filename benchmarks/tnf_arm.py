@@ -70,3 +70,43 @@ def run(ctx, total_bp: int, steps: int, warmup: int, hbm_gbs: float, threads: in
         "host_generate_s": gen_s, "host_pack_s": pack_s,
         "sample": (seq, offs),
     }
+
+
+def run_sharded(ctx, total_bp: int, steps: int, rank: int, world: int, threads: int):
+    """TNF counting on `world` ranks: the records are split into contiguous ranges of equal bases, one
+    per rank; every rank uploads its own range over its own PCIe link and counts it — no exchange, the outputs are
+    disjoint row ranges.  Each rank synthesises its own range (same generator, rank-dependent seed).  Collective (the
+    barrier).  -> dict on every rank; `value` is the aggregate end-to-end Gbp/s (all bases / slowest rank)."""
+    import torch
+    import torch.distributed as dist
+
+    import oracle
+    from rosella_b200 import synth
+
+    seq, offs = synth.contigs(total_bp // world, seed=synth.SEED_TNF + 1000 * world + rank, threads=threads)
+    bases = int(offs[-1])
+    pin = torch.empty(len(seq), dtype=torch.uint8, pin_memory=True)
+    pin.numpy()[:] = seq
+    seq_pin = pin.numpy()
+    counts, nk, _ = ctx.tnf_count_ascii(seq_pin, offs)          # warm-up + parity on a prefix of this rank's range
+    cut = min(len(offs) - 1, 400)
+    wc, wnk, _ = oracle.tnf_count(seq, offs[:cut + 1], fast=True, threads=threads)
+    ok = bool(np.array_equal(counts[:cut], wc) and np.array_equal(nk[:cut], wnk))
+    times = []
+    for _ in range(max(steps, 2)):
+        torch.cuda.synchronize()
+        dist.barrier()
+        t = time.perf_counter()
+        ctx.tnf_count_ascii(seq_pin, offs)
+        times.append(time.perf_counter() - t)
+    tm = ctx.timings()
+    loc = torch.tensor([float(np.mean(times)), float(bases), tm["tnf_count_ms"], 0.0 if ok else 1.0], dtype=torch.float64, device="cuda")
+    mx = loc.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = loc.clone()
+    dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    return {"value": float(sm[1]) / float(mx[0]) / 1e9, "unit": "Gbp/s", "bases": int(sm[1]), "ranks": world,
+            "seconds_slowest_rank": float(mx[0]), "ascii_kernel_ms_slowest_rank": float(mx[2]),
+            "bit_exact_vs_oracle_prefix": bool(float(mx[3]) == 0.0),
+            "what": "end to end through rg_tnf_count_ascii on every rank: pinned host ASCII of the rank's own contiguous "
+                    "range -> counts / n_kmers / freqs on the host; no exchange"}

@@ -20,9 +20,10 @@
  *   - NO CPU FALLBACK: without an sm_100 device rg_create fails with RG_ERR_NO_DEVICE.
  *   - a handle serves one caller thread at a time (the reference calls both entry points from
  *     its single pipeline thread, recover_engine.rs:111,:510).
- *   - one handle = one GPU.  Multi-GPU = one handle (process) per GPU, query rows sharded with
- *     [q_begin, q_end); the per-rank slabs are concatenated by the caller (NCCL all-gather on the
- *     *_dev outputs, or host concatenation).
+ *   - one handle = one GPU.  More GPUs, all inside the library (NCCL over NVLink, dlopen'ed on first use):
+ *       rg_multi_*        one process, one caller thread, n GPUs — what EmbedderEngine::build_mutual_kgraph's single
+ *                         pipeline thread (recover_engine.rs:510-519) binds;
+ *       rg_comm_* + rg_knn_load_dist / rg_knn_build_dist   one process per GPU (MPI / torchrun style launchers).
  */
 #ifndef ROSELLA_GPU_H
 #define ROSELLA_GPU_H
@@ -163,6 +164,69 @@ int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const double *cov, 
                             uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges,
                             uint64_t *offsets, uint32_t *neighbours, float *weights,
                             uint64_t *n_disconnected, uint32_t *disconnected);
+
+/* The lists of the last rg_knn_build_mutual stay on the handle: the reference calls build_mutual_kgraph again with
+ * only keep_n_edges changed (prefilter_nodes, recover_engine.rs:464-482; the embed retry loop, :438-459).  This
+ * re-applies intersect + mutual_knn to the kept lists — no load, no search.  RG_ERR_STATE without kept lists. */
+int32_t rg_knn_refilter(rg_handle *h, uint32_t keep_n_edges, uint64_t *offsets, uint32_t *neighbours, float *weights,
+                        uint64_t *n_disconnected, uint32_t *disconnected);
+
+/* build_mutual_kgraph of a SUBSET of the rows (evaluate_subset, recover_engine.rs:410-435: retrieve_contig_data
+ * gathers the rows of the given indices, :522-543).  row_ids: m distinct rows of the n-row tables; the graph is
+ * built over those m rows only and its node numbers are POSITIONS in row_ids (the caller maps them back exactly as
+ * recover_engine.rs:422 does with get_data_id_from_idx).  Outputs as rg_knn_build (m x k per graph). */
+int32_t rg_knn_build_subset(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
+                            const uint64_t *row_ids, uint64_t m, uint32_t k, uint32_t variant, uint32_t which_mask,
+                            uint32_t *tnf_idx, float *tnf_dist, uint32_t *depth_idx, float *depth_dist);
+
+/* ------------------------------------------------------------------ more than one GPU */
+/* (a) One process per GPU.  Rank 0 makes an id and hands it to the others by any means (file, MPI, torch.distributed);
+ * every rank then joins with its own handle.  All calls below are COLLECTIVE: every rank makes them in the same order.
+ * A rank that fails before a collective makes every rank return an error (a status word is agreed on first). */
+#define RG_COMM_ID_BYTES 128
+int32_t rg_comm_unique_id(uint8_t id[RG_COMM_ID_BYTES]);
+int32_t rg_comm_init(rg_handle *h, int32_t rank, int32_t world, const uint8_t id[RG_COMM_ID_BYTES]);
+int32_t rg_comm_destroy(rg_handle *h);
+/* rows [*begin, *end) of an n-row graph that rank owns (whole 32-row tiles, sizes differ by at most one tile) */
+int32_t rg_comm_shard(uint64_t n, int32_t rank, int32_t world, uint64_t *begin, uint64_t *end);
+/* rg_knn_load across the communicator: only `root` reads its host tables (the others may pass NULL for a table the
+ * root passes); the f64 tables travel by ncclBroadcast over NVLink instead of one PCIe upload per rank. */
+int32_t rg_knn_load_dist(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
+                         uint32_t variant, int32_t root);
+/* Whole graph `which` of the loaded tables on all ranks.  Coverage graph: symmetric block build, every unordered
+ * pair evaluated once on one rank, partial K' lists exchanged all-to-all (ncclSend/Recv), merged, re-evaluated in f64
+ * on the owner of the row; TNF graphs: query-row shards.  gather = 1: idx / dist (n x k) are complete on every rank
+ * (in-place all-gather of the slabs); gather = 0: only this rank's rows [begin, end) are written.
+ * *_dev: device pointers, asynchronous on rg_stream(h).  Host flavour: pageable or pinned host arrays, synchronous. */
+int32_t rg_knn_build_dist_dev(rg_handle *h, uint32_t which, uint32_t k, uint32_t gather, uint32_t *idx_dev, float *dist_dev);
+int32_t rg_knn_build_dist(rg_handle *h, uint32_t which, uint32_t k, uint32_t gather, uint32_t *idx, float *dist);
+typedef struct {
+    double load_h2d_ms, load_bcast_ms, load_transform_ms;   /* last rg_knn_load_dist */
+    double partial_ms;      /* last coverage build: this rank's share of the row blocks (evaluation + list reducers) */
+    double exchange_ms;     /* all-to-all of the partial lists */
+    double finish_ms;       /* merge + f64 re-evaluation + certificate (TNF graphs: select + re-evaluation) */
+    double gather_ms;       /* all-gather of the finished slabs / device->host copy of this rank's slab */
+} rg_dist_timings;
+int32_t rg_get_dist_timings(rg_handle *h, rg_dist_timings *out);
+
+/* (b) One process, one caller thread, n_dev GPUs: one worker thread and one handle per device inside the library,
+ * communicator made with ncclCommInitAll.  The calls mirror the single-GPU ones and return the same results;
+ * rg_multi_tnf_count_ascii splits the records into n_dev contiguous ranges of equal bases (no exchange, every GPU
+ * uploads its own range over its own PCIe link). */
+typedef struct rg_multi rg_multi;
+int32_t rg_multi_create(const int32_t *device_ids, int32_t n_dev, rg_multi **out);
+void rg_multi_destroy(rg_multi *m);
+const char *rg_multi_last_error(const rg_multi *m);
+int32_t rg_multi_size(const rg_multi *m);
+rg_handle *rg_multi_handle(rg_multi *m, int32_t i);     /* options, timings; do not issue work on it while m runs */
+int32_t rg_multi_knn_build(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
+                           uint32_t k, uint32_t variant, uint32_t which_mask, uint32_t *tnf_idx, float *tnf_dist,
+                           uint32_t *depth_idx, float *depth_dist);
+int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                                  uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges, uint64_t *offsets,
+                                  uint32_t *neighbours, float *weights, uint64_t *n_disconnected, uint32_t *disconnected);
+int32_t rg_multi_tnf_count_ascii(rg_multi *m, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t *counts,
+                                 uint64_t *n_kmers, double *freqs);
 
 /* ------------------------------------------------------------------ graph post-ops */
 /* keep[i*k+j] = 1 when edge j of node i survives mutual_knn / intersect

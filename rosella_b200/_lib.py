@@ -21,6 +21,11 @@ SYMBOLS = [
     "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
+    "rg_knn_refilter", "rg_knn_build_subset",
+    "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
+    "rg_knn_build_dist", "rg_get_dist_timings",
+    "rg_multi_create", "rg_multi_destroy", "rg_multi_last_error", "rg_multi_size", "rg_multi_handle", "rg_multi_knn_build",
+    "rg_multi_knn_build_mutual", "rg_multi_tnf_count_ascii",
 ]
 
 
@@ -29,6 +34,14 @@ class Timings(C.Structure):
                 ("rescore_ms", C.c_double), ("d2h_ms", C.c_double), ("tnf_count_ms", C.c_double),
                 ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("rows_flagged", C.c_uint64), ("rows_exact", C.c_uint64), ("extra_pairs", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class DistTimings(C.Structure):
+    _fields_ = [("load_h2d_ms", C.c_double), ("load_bcast_ms", C.c_double), ("load_transform_ms", C.c_double),
+                ("partial_ms", C.c_double), ("exchange_ms", C.c_double), ("finish_ms", C.c_double), ("gather_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -85,6 +98,27 @@ def load() -> C.CDLL:
         "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
         "rg_knn_flagged_rows": (C.c_int32, [vp, u32p, f32p, f32p, C.c_uint64, C.POINTER(C.c_uint64)]),
+        "rg_knn_refilter": (C.c_int32, [vp, C.c_uint32, u64p, u32p, f32p, u64p, u32p]),
+        "rg_knn_build_subset": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, u64p, C.c_uint64, C.c_uint32,
+                                            C.c_uint32, C.c_uint32, u32p, f32p, u32p, f32p]),
+        "rg_comm_unique_id": (C.c_int32, [u8p]),
+        "rg_comm_init": (C.c_int32, [vp, C.c_int32, C.c_int32, u8p]),
+        "rg_comm_destroy": (C.c_int32, [vp]),
+        "rg_comm_shard": (C.c_int32, [C.c_uint64, C.c_int32, C.c_int32, u64p, u64p]),
+        "rg_knn_load_dist": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32]),
+        "rg_knn_build_dist_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
+        "rg_knn_build_dist": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, u32p, f32p]),
+        "rg_get_dist_timings": (C.c_int32, [vp, C.POINTER(DistTimings)]),
+        "rg_multi_create": (C.c_int32, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]),
+        "rg_multi_destroy": (None, [vp]),
+        "rg_multi_last_error": (C.c_char_p, [vp]),
+        "rg_multi_size": (C.c_int32, [vp]),
+        "rg_multi_handle": (vp, [vp, C.c_int32]),
+        "rg_multi_knn_build": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                           C.c_uint32, u32p, f32p, u32p, f32p]),
+        "rg_multi_knn_build_mutual": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                                  C.c_uint32, u64p, u32p, f32p, u64p, u32p]),
+        "rg_multi_tnf_count_ascii": (C.c_int32, [vp, u8p, u64p, C.c_uint64, u32p, u64p, f64p]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

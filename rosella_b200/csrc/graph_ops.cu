@@ -2,6 +2,8 @@
 // :38-72): per edge, keep it if it is among the first keep_n_edges of its node, else only if the
 // reverse edge exists in the same / the other graph.  The reference discards these lists
 // (SURVEY F5); the caller decides whether to apply the mask.
+#include <cstdlib>
+
 #include "rg_internal.cuh"
 
 namespace {
@@ -135,34 +137,34 @@ __global__ void compact_kernel(const uint32_t *__restrict__ idx, const float *__
 
 }  // namespace
 
-extern "C" int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
-                                       uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges,
-                                       uint64_t *offsets, uint32_t *neighbours, float *weights,
-                                       uint64_t *n_disconnected, uint32_t *disconnected) {
-    if (!h) return RG_ERR_INVALID;
-    if (!tnf || !cov || !offsets || !neighbours || !weights)
-        return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_mutual: NULL pointer");
-    RG_TRY(rg_knn_load(h, tnf, cov, n, d, s, variant));
+// intersect + mutual_knn + CSR of the lists kept on the handle (cache_di / cache_dd: coverage graph, cache_ti: TNF
+// graph, [n][cache_k]); host outputs.  Shared by rg_knn_build_mutual, rg_knn_refilter and rg_multi_knn_build_mutual.
+int32_t rg_filter_cached_lists(rg_handle *h, uint32_t keep_n_edges, uint64_t *offsets, uint32_t *neighbours,
+                               float *weights, uint64_t *n_disconnected, uint32_t *disconnected) {
+    if (h->lists_cached != 3) return rg_fail(h, RG_ERR_STATE, "no kNN lists are kept on the handle (call rg_knn_build_mutual first)");
+    if (!offsets || !neighbours || !weights) return rg_fail(h, RG_ERR_INVALID, "graph filter: NULL output pointer");
+    RG_CUDA(h, cudaSetDevice(h->device));
+    const uint64_t n = h->n;
+    const uint32_t k = h->cache_k;
     const uint64_t edges = n * k;
-    DevBuf di, dd, ti, td, k1, k2, cnt, off, tmp, on, ow;
+    const uint32_t *di = (const uint32_t *)h->cache_di.p, *ti = (const uint32_t *)h->cache_ti.p;
+    const float *dd = (const float *)h->cache_dd.p;
+    DevBuf k1, k2, cnt, off, tmp, on, ow;
     auto done = [&](int32_t rc) {
-        for (DevBuf *b : {&di, &dd, &ti, &td, &k1, &k2, &cnt, &off, &tmp, &on, &ow}) rg_release(*b);
+        for (DevBuf *b : {&k1, &k2, &cnt, &off, &tmp, &on, &ow}) rg_release(*b);
         return rc;
     };
 #define RG_TRY_D(expr) do { int32_t rc__ = (expr); if (rc__ != RG_OK) return done(rc__); } while (0)
 #define RG_CUDA_D(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return done(rg_fail(h, RG_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__))); } while (0)
-    RG_TRY_D(rg_reserve(h, di, edges * 4)); RG_TRY_D(rg_reserve(h, dd, edges * 4));
-    RG_TRY_D(rg_reserve(h, ti, edges * 4)); RG_TRY_D(rg_reserve(h, td, edges * 4));
     RG_TRY_D(rg_reserve(h, k1, edges)); RG_TRY_D(rg_reserve(h, k2, edges));
     RG_TRY_D(rg_reserve(h, cnt, (n + 1) * 8)); RG_TRY_D(rg_reserve(h, off, (n + 1) * 8));
-    RG_TRY_D(rg_knn_search_dev(h, RG_GRAPH_DEPTH, k, 0, n, (uint32_t *)di.p, (float *)dd.p, nullptr));   // embedder.rs:32-65
-    RG_TRY_D(rg_knn_search_dev(h, RG_GRAPH_TNF, k, 0, n, (uint32_t *)ti.p, (float *)td.p, nullptr));
     const uint32_t keep_first = keep_n_edges > 5u ? keep_n_edges : 5u;                                    // DEFAULT_KEEP_N_EDGES
-    edge_keep_kernel<<<(unsigned)((edges + 255) / 256), 256, 0, h->stream>>>((const uint32_t *)di.p, (const uint32_t *)ti.p,
-                                                                            n, k, keep_first, (uint8_t *)k1.p);
+    edge_keep_kernel<<<(unsigned)((edges + 255) / 256), 256, 0, h->stream>>>(di, ti, n, k, keep_first, (uint8_t *)k1.p);
+    RG_CUDA_D(cudaGetLastError());
     RG_CUDA_D(cudaMemsetAsync(cnt.p, 0, (n + 1) * 8, h->stream));
     mutual_after_intersect_kernel<<<(unsigned)((n + 127) / 128), 128, 0, h->stream>>>(
-        (const uint32_t *)di.p, (const uint8_t *)k1.p, n, k, keep_n_edges, (uint8_t *)k2.p, (uint64_t *)cnt.p);
+        di, (const uint8_t *)k1.p, n, k, keep_n_edges, (uint8_t *)k2.p, (uint64_t *)cnt.p);
+    RG_CUDA_D(cudaGetLastError());
     size_t tmp_bytes = 0;
     RG_CUDA_D(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, (const uint64_t *)cnt.p, (uint64_t *)off.p, (int64_t)(n + 1), h->stream));
     RG_TRY_D(rg_reserve(h, tmp, tmp_bytes ? tmp_bytes : 8));
@@ -171,11 +173,10 @@ extern "C" int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const do
     RG_CUDA_D(cudaStreamSynchronize(h->stream));
     const uint64_t total = offsets[n];
     RG_TRY_D(rg_reserve(h, on, (total ? total : 1) * 4)); RG_TRY_D(rg_reserve(h, ow, (total ? total : 1) * 4));
-    compact_kernel<<<(unsigned)((n + 127) / 128), 128, 0, h->stream>>>((const uint32_t *)di.p, (const float *)dd.p,
-                                                                      (const uint8_t *)k2.p, (const uint64_t *)off.p, n, k,
+    compact_kernel<<<(unsigned)((n + 127) / 128), 128, 0, h->stream>>>(di, dd, (const uint8_t *)k2.p, (const uint64_t *)off.p, n, k,
                                                                       (uint32_t *)on.p, (float *)ow.p);
     RG_CUDA_D(cudaGetLastError());
-    h->tm.kernel_launches += 4;
+    h->tm.kernel_launches += 3;
     if (total) {
         RG_CUDA_D(cudaMemcpyAsync(neighbours, on.p, total * 4, cudaMemcpyDeviceToHost, h->stream));
         RG_CUDA_D(cudaMemcpyAsync(weights, ow.p, total * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -192,4 +193,64 @@ extern "C" int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const do
 #undef RG_TRY_D
 #undef RG_CUDA_D
     return done(RG_OK);
+}
+
+// reserve the kept lists for n rows x k (both graphs)
+int32_t rg_reserve_list_cache(rg_handle *h, uint64_t n, uint32_t k) {
+    h->lists_cached = 0;
+    RG_TRY(rg_reserve(h, h->cache_di, n * k * 4)); RG_TRY(rg_reserve(h, h->cache_dd, n * k * 4));
+    RG_TRY(rg_reserve(h, h->cache_ti, n * k * 4)); RG_TRY(rg_reserve(h, h->cache_td, n * k * 4));
+    h->cache_k = k;
+    return RG_OK;
+}
+
+extern "C" int32_t rg_knn_build_mutual(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                                       uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges,
+                                       uint64_t *offsets, uint32_t *neighbours, float *weights,
+                                       uint64_t *n_disconnected, uint32_t *disconnected) {
+    if (!h) return RG_ERR_INVALID;
+    if (!tnf || !cov || !offsets || !neighbours || !weights)
+        return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_mutual: NULL pointer");
+    RG_TRY(rg_knn_load(h, tnf, cov, n, d, s, variant));
+    RG_TRY(rg_reserve_list_cache(h, n, k));
+    RG_TRY(rg_knn_search_dev(h, RG_GRAPH_DEPTH, k, 0, n, (uint32_t *)h->cache_di.p, (float *)h->cache_dd.p, nullptr));   // embedder.rs:32-65
+    RG_TRY(rg_knn_search_dev(h, RG_GRAPH_TNF, k, 0, n, (uint32_t *)h->cache_ti.p, (float *)h->cache_td.p, nullptr));
+    h->lists_cached = 3;
+    return rg_filter_cached_lists(h, keep_n_edges, offsets, neighbours, weights, n_disconnected, disconnected);
+}
+
+extern "C" int32_t rg_knn_refilter(rg_handle *h, uint32_t keep_n_edges, uint64_t *offsets, uint32_t *neighbours,
+                                   float *weights, uint64_t *n_disconnected, uint32_t *disconnected) {
+    if (!h) return RG_ERR_INVALID;
+    return rg_filter_cached_lists(h, keep_n_edges, offsets, neighbours, weights, n_disconnected, disconnected);
+}
+
+// evaluate_subset (recover_engine.rs:410-435): the rows of row_ids are gathered (retrieve_contig_data, :522-543) and
+// the graph of those rows alone is built; node numbers are positions in row_ids
+extern "C" int32_t rg_knn_build_subset(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                                       uint32_t s, const uint64_t *row_ids, uint64_t m, uint32_t k, uint32_t variant,
+                                       uint32_t which_mask, uint32_t *tnf_idx, float *tnf_dist, uint32_t *depth_idx,
+                                       float *depth_dist) {
+    if (!h) return RG_ERR_INVALID;
+    if (!row_ids) return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_subset: row_ids is NULL");
+    const bool want_tnf = which_mask & (1u << RG_GRAPH_TNF), want_depth = which_mask & (1u << RG_GRAPH_DEPTH);
+    if ((want_tnf && !tnf) || (want_depth && !cov)) return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_subset: a requested graph has a NULL table");
+    for (uint64_t i = 0; i < m; ++i)
+        if (row_ids[i] >= n) return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_subset: row_ids[%llu] = %llu is outside [0,%llu)",
+                                            (unsigned long long)i, (unsigned long long)row_ids[i], (unsigned long long)n);
+    double *sub_tnf = nullptr, *sub_cov = nullptr;
+    const size_t wt = d, wc = 2 * (size_t)s;
+    if (want_tnf) sub_tnf = (double *)malloc((m ? m : 1) * wt * sizeof(double));
+    if (want_depth) sub_cov = (double *)malloc((m ? m : 1) * wc * sizeof(double));
+    if ((want_tnf && !sub_tnf) || (want_depth && !sub_cov)) {
+        free(sub_tnf); free(sub_cov);
+        return rg_fail(h, RG_ERR_OOM, "rg_knn_build_subset: host allocation for %llu gathered rows failed", (unsigned long long)m);
+    }
+    for (uint64_t i = 0; i < m; ++i) {
+        if (want_tnf) memcpy(sub_tnf + i * wt, tnf + row_ids[i] * wt, wt * sizeof(double));
+        if (want_depth) memcpy(sub_cov + i * wc, cov + row_ids[i] * wc, wc * sizeof(double));
+    }
+    const int32_t rc = rg_knn_build(h, sub_tnf, sub_cov, m, d, s, k, variant, which_mask, tnf_idx, tnf_dist, depth_idx, depth_dist);
+    free(sub_tnf); free(sub_cov);
+    return rc;
 }

@@ -118,43 +118,46 @@ int32_t rg_ensure_tnf_tiles(rg_handle *h) {
     return RG_OK;
 }
 
-extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
-                               uint32_t s, uint32_t variant) {
+// rg_knn_load in three phases, shared with the broadcast-fed load of the multi-GPU build (knn_dist.cu):
+//   rg_knn_load_begin   validate, reserve every buffer                        (no table data needed)
+//   (fill h->tnf64 / h->cov64: H2D copy here, ncclBroadcast from the root rank there)
+//   rg_knn_load_finish  pre-transform kernels, input checks, collision patches; publishes the shape on the handle
+int32_t rg_knn_load_begin(rg_handle *h, bool has_tnf, bool has_cov, uint64_t n, uint32_t d, uint32_t s, uint32_t variant) {
     if (!h) return RG_ERR_INVALID;
-    if (!tnf && !cov) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: both tables are NULL");
+    if (!has_tnf && !has_cov) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: both tables are NULL");
     if (n < 2) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: need at least 2 rows, got %llu", (unsigned long long)n);
     if (n >= 0xffffffffull) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: n must be < 2^32-1");
-    if (tnf && (d == 0 || d % 4 != 0 || d > 256))
+    if (has_tnf && (d == 0 || d % 4 != 0 || d > 256))
         return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: d=%u must be a multiple of 4 in (0,256] (TNF has 136 bins)", d);
-    if (cov && (s == 0 || s > 4096)) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: s=%u out of range [1,4096]", s);
+    if (has_cov && (s == 0 || s > 4096)) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: s=%u out of range [1,4096]", s);
     if (variant > RG_VARIANT_FLIGHT) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load: unknown variant %u", variant);
     RG_CUDA(h, cudaSetDevice(h->device));
     h->n = 0;
     h->has_tnf = h->has_cov = false;
-    const uint64_t n_tiles = (n + RG_TILE - 1) / RG_TILE;
-    const uint64_t n_panels = (n + RG_PANEL - 1) / RG_PANEL;
-    const uint64_t rows_padded = n_panels * RG_PANEL;   // whole 128-row panels (a multiple of the 32-row tiles)
+    h->lists_cached = 0;
+    const uint64_t rows_padded = (n + RG_PANEL - 1) / RG_PANEL * RG_PANEL;   // whole 128-row panels (a multiple of the 32-row tiles)
     RG_TRY(rg_reserve(h, h->err_flag, sizeof(uint32_t)));
-    RG_CUDA(h, cudaMemsetAsync(h->err_flag.p, 0, sizeof(uint32_t), h->stream));
-
-    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
-    if (tnf) {
+    if (has_tnf) {
         RG_TRY(rg_reserve(h, h->tnf64, n * d * sizeof(double)));
         RG_TRY(rg_reserve(h, h->tnf_norm, rows_padded * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_mean, rows_padded * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_hi, rows_padded * d * sizeof(float)));
         RG_TRY(rg_reserve(h, h->tnf_lo, rows_padded * d * sizeof(float)));
-        RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-        h->tm.h2d_bytes += n * d * sizeof(double);
     }
-    if (cov) {
+    if (has_cov) {
         RG_TRY(rg_reserve(h, h->cov64, n * 2 * s * sizeof(double)));
         RG_TRY(rg_reserve(h, h->cov_t, rows_padded * s * sizeof(float4)));
-        RG_CUDA(h, cudaMemcpyAsync(h->cov64.p, cov, n * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-        h->tm.h2d_bytes += n * 2 * s * sizeof(double);
     }
+    return RG_OK;
+}
+
+int32_t rg_knn_load_finish(rg_handle *h, bool has_tnf, bool has_cov, uint64_t n, uint32_t d, uint32_t s, uint32_t variant) {
+    const uint64_t n_tiles = (n + RG_TILE - 1) / RG_TILE;
+    const uint64_t n_panels = (n + RG_PANEL - 1) / RG_PANEL;
+    const uint64_t rows_padded = n_panels * RG_PANEL;
+    RG_CUDA(h, cudaMemsetAsync(h->err_flag.p, 0, sizeof(uint32_t), h->stream));
     RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
-    if (tnf) {
+    if (has_tnf) {
         const int wpb = 8;
         tnf_transform_kernel<<<(unsigned)((rows_padded + wpb - 1) / wpb), wpb * 32, 0, h->stream>>>(
             (const double *)h->tnf64.p, n, d, nullptr, (float *)h->tnf_norm.p, (float *)h->tnf_mean.p,
@@ -162,7 +165,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
         RG_CUDA(h, cudaGetLastError());
         h->tm.kernel_launches += 1;
     }
-    if (cov) {
+    if (has_cov) {
         const uint64_t total = rows_padded * s;
         unsigned blocks = (unsigned)((total + 255) / 256);
         const unsigned cap = (unsigned)h->sm_count * 32u;
@@ -176,7 +179,6 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     uint32_t flag = 0;
     RG_CUDA(h, cudaMemcpyAsync(&flag, h->err_flag.p, sizeof(flag), cudaMemcpyDeviceToHost, h->stream));
     RG_CUDA(h, cudaStreamSynchronize(h->stream));
-    h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
     h->tm.transform_ms = rg_elapsed(h->ev[1], h->ev[2]);
     if (flag & 1u)
         return rg_fail(h, RG_ERR_INVALID,
@@ -190,7 +192,7 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
     h->n_extra = 0;
     h->tnf_t_valid = false;
     if (h->cert_ctr.p) RG_CUDA(h, cudaMemsetAsync(h->cert_ctr.p, 0, 8 * sizeof(uint32_t), h->stream));
-    if (cov && h->opt_certify) {
+    if (has_cov && h->opt_certify) {
         RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
         RG_TRY(rg_build_collision_patches(h, n, s, variant));
         RG_CUDA(h, cudaEventRecord(h->ev[2], h->stream));
@@ -198,7 +200,25 @@ extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *co
         h->tm.transform_ms += rg_elapsed(h->ev[1], h->ev[2]);
     }
     h->n = n; h->d = d; h->s = s; h->variant = variant; h->n_tiles = n_tiles; h->n_panels = n_panels;
-    h->has_tnf = tnf != nullptr;
-    h->has_cov = cov != nullptr;
+    h->has_tnf = has_tnf;
+    h->has_cov = has_cov;
     return RG_OK;
+}
+
+extern "C" int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
+                               uint32_t s, uint32_t variant) {
+    RG_TRY(rg_knn_load_begin(h, tnf != nullptr, cov != nullptr, n, d, s, variant));
+    RG_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    if (tnf) {
+        RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->tm.h2d_bytes += n * d * sizeof(double);
+    }
+    if (cov) {
+        RG_CUDA(h, cudaMemcpyAsync(h->cov64.p, cov, n * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->tm.h2d_bytes += n * 2 * s * sizeof(double);
+    }
+    RG_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    RG_CUDA(h, cudaEventSynchronize(h->ev[1]));
+    h->tm.h2d_ms = rg_elapsed(h->ev[0], h->ev[1]);
+    return rg_knn_load_finish(h, tnf != nullptr, cov != nullptr, n, d, s, variant);
 }

@@ -58,6 +58,20 @@ struct rg_handle {
     uint64_t n_extra = 0;     // directed extra candidate pairs found by the last load
     bool has_extra = false;
 
+    // ---- multi-GPU (rg_comm.cu, knn_dist.cu): one handle = one rank of an NCCL communicator
+    void *comm = nullptr;             // ncclComm_t (NCCL is dlopen'ed on first use; single-GPU callers never need it)
+    int rank = 0, world = 1;
+    DevBuf dist_pd, dist_pi;          // this rank's partial lists of ALL rows [n][K'] (symmetric coverage build)
+    DevBuf dist_rd, dist_ri;          // all ranks' partial lists of this rank's rows [world][rows][K']
+    DevBuf dist_status;               // i32 status word agreed on before a collective is entered
+    cudaEvent_t dist_ev[8] = {};
+    rg_dist_timings dtm = {};
+
+    // ---- kNN lists kept for rg_knn_refilter (graph_ops.cu)
+    DevBuf cache_di, cache_dd, cache_ti, cache_td;
+    uint32_t cache_k = 0;
+    int lists_cached = 0;
+
     // ---- options (rg_set_option); the library never reads the environment
     int opt_depth_build = 0;          // 0 = automatic, 1 = batch kernel, 2 = symmetric block build
     uint64_t opt_sym_block = 0, opt_sym_chunk = 0;   // rows per block / columns per launch of the symmetric build (0 = default)

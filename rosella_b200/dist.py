@@ -1,5 +1,12 @@
-"""Multi-GPU host logic: one process per GPU, query rows sharded, references replicated, one
-all-gather of the per-rank slabs.  Backend-agnostic: NCCL on GPUs, gloo in the CPU tests."""
+"""One process per GPU (torchrun-style launchers) on top of the C ABI.
+
+Product path: `init_comm` + `build_graph` — the exchange itself (ncclSend/Recv all-to-all of partial lists, merge, f64
+finish, in-place all-gather) runs INSIDE librosella_gpu.so (rg_knn_build_dist, csrc/knn_dist.cu); torch.distributed only
+carries the 128-byte communicator id and the bench's barriers.
+
+The functions below `# ---- host-side model` restate the same exchange with torch collectives.  They are what the
+world-size-2 gloo tests run on CPU (layout of the all-to-all, the merge input, uneven shards) and are not on the
+product path."""
 from __future__ import annotations
 
 import numpy as np
@@ -17,6 +24,36 @@ def shard_range(n: int, rank: int, world: int, align: int = TILE) -> tuple[int, 
     return min(t0 * align, n), min(t1 * align, n)
 
 
+def init_comm(ctx, rank: int, world: int, group=None):
+    """rg_comm_init on every rank: rank 0's ncclUniqueId travels through torch.distributed (any backend)."""
+    import torch
+    import torch.distributed as dist
+    from . import gpu
+    if world == 1:
+        return
+    on_gpu = dist.get_backend(group) == "nccl"
+    uid = torch.from_numpy(gpu.comm_unique_id() if rank == 0 else np.zeros(128, np.uint8))
+    if on_gpu:
+        uid = uid.cuda()
+    dist.broadcast(uid, src=0, group=group)
+    ctx.comm_init(rank, world, uid.cpu().numpy())
+
+
+def build_graph(ctx, which: int, k: int, n: int, gather: bool = True):
+    """rg_knn_build_dist_dev: the whole graph `which` over the communicator of ctx (collective).
+    -> (idx int32 [n,k], dist float32 [n,k]) torch tensors on the rank's device; gather=False leaves other ranks'
+    rows unwritten."""
+    import torch
+    dev = torch.device("cuda", ctx.device)
+    idx = torch.empty((n, k), dtype=torch.int32, device=dev)
+    dst = torch.empty((n, k), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize(dev)          # the buffers come from torch's stream, the library works on ctx.stream
+    ctx.knn_build_dist_dev(which, k, gather, idx.data_ptr(), dst.data_ptr())
+    ctx.sync()
+    return idx, dst
+
+
+# ---- host-side model of the exchange (CPU tests)
 def all_gather_rows(local, n: int, world: int, group=None):
     """all-gather row blocks of unequal length (shard_range) into an [n, k] tensor on every rank."""
     import torch
@@ -38,6 +75,7 @@ def build_graph_distributed(ctx, which: int, k: int, n: int, rank: int, world: i
     dev = torch.device("cuda", ctx.device)
     idx = torch.empty((qe - qb, k), dtype=torch.int32, device=dev)
     dst = torch.empty((qe - qb, k), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize(dev)      # the buffers above come from torch's stream; the work below runs on ctx.stream
     if qe > qb:
         ctx.knn_search_dev(which, k, qb, qe, idx.data_ptr(), dst.data_ptr())
     ext = torch.cuda.ExternalStream(ctx.stream, device=ctx.device)
@@ -94,6 +132,3 @@ def build_depth_graph_symmetric(ctx, k: int, n: int, rank: int, world: int):
     ctx.sync()
     return idx, dst
 
-
-def concat_host(parts: list[np.ndarray]) -> np.ndarray:
-    return np.concatenate(parts, axis=0)

@@ -7,9 +7,10 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import GRAPH_DEPTH, GRAPH_TNF, GRAPH_TNF_EUCLID, NBINS, VARIANT_FLIGHT, VARIANT_RUST, RosellaGpuError, Timings
+from ._lib import (GRAPH_DEPTH, GRAPH_TNF, GRAPH_TNF_EUCLID, NBINS, VARIANT_FLIGHT, VARIANT_RUST, DistTimings, RosellaGpuError,
+                   Timings)
 
-__all__ = ["Context", "canonical_kmers", "pack_host", "GRAPH_TNF", "GRAPH_DEPTH", "GRAPH_TNF_EUCLID", "VARIANT_RUST", "VARIANT_FLIGHT"]
+__all__ = ["Context", "Multi", "comm_unique_id", "comm_shard", "canonical_kmers", "pack_host", "GRAPH_TNF", "GRAPH_DEPTH", "GRAPH_TNF_EUCLID", "VARIANT_RUST", "VARIANT_FLIGHT"]
 
 
 def canonical_kmers() -> list[str]:
@@ -37,9 +38,31 @@ def pack_host(seq: np.ndarray, offsets: np.ndarray, threads: int = 0):
     return codes[:words], valid[:words], woff
 
 
+def comm_unique_id() -> np.ndarray:
+    """rg_comm_unique_id: 128 bytes that rank 0 hands to the other ranks (file, MPI, torch.distributed ...)."""
+    buf = np.zeros(128, np.uint8)
+    rc = _lib.load().rg_comm_unique_id(_lib.ptr(buf, C.c_uint8))
+    if rc:
+        raise RosellaGpuError(rc, (_lib.load().rg_last_error(None) or b"").decode())
+    return buf
+
+
+def comm_shard(n: int, rank: int, world: int) -> tuple[int, int]:
+    b, e = C.c_uint64(0), C.c_uint64(0)
+    rc = _lib.load().rg_comm_shard(n, rank, world, C.byref(b), C.byref(e))
+    if rc:
+        raise RosellaGpuError(rc, "rg_comm_shard")
+    return int(b.value), int(e.value)
+
+
 class Context:
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _borrowed=None):
         self.lib = _lib.load()
+        self._owned = _borrowed is None
+        if _borrowed is not None:        # a handle that belongs to an rg_multi (options / timings only)
+            self.h = C.c_void_p(_borrowed)
+            self.device = device
+            return
         h = C.c_void_p()
         rc = self.lib.rg_create(device, C.byref(h))
         if rc:
@@ -48,9 +71,9 @@ class Context:
         self.device = device
 
     def close(self):
-        if getattr(self, "h", None):
+        if getattr(self, "h", None) and self._owned:
             self.lib.rg_destroy(self.h)
-            self.h = None
+        self.h = None
 
     __del__ = close
 
@@ -157,6 +180,7 @@ class Context:
         disconnected u32[...])"""
         tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
         n, d, s = tnf.shape[0], tnf.shape[1], cov.shape[1] // 2
+        self._n = n
         off = np.zeros(n + 1, np.uint64)
         nbr, w = np.zeros(n * k, np.uint32), np.zeros(n * k, np.float32)
         disc, nd = np.zeros(n, np.uint32), C.c_uint64(0)
@@ -165,6 +189,69 @@ class Context:
                                                _lib.ptr(w, C.c_float), C.byref(nd), _lib.ptr(disc, C.c_uint32)))
         e = int(off[-1])
         return off, nbr[:e].copy(), w[:e].copy(), disc[:nd.value].copy()
+
+    def knn_refilter(self, keep_n_edges: int, k: int):
+        """intersect + mutual_knn re-applied to the lists of the last knn_build_mutual (no load, no search)."""
+        n = self._n
+        off = np.zeros(n + 1, np.uint64)
+        nbr, w = np.zeros(n * k, np.uint32), np.zeros(n * k, np.float32)
+        disc, nd = np.zeros(n, np.uint32), C.c_uint64(0)
+        self._chk(self.lib.rg_knn_refilter(self.h, keep_n_edges, _lib.ptr(off, C.c_uint64), _lib.ptr(nbr, C.c_uint32),
+                                           _lib.ptr(w, C.c_float), C.byref(nd), _lib.ptr(disc, C.c_uint32)))
+        e = int(off[-1])
+        return off, nbr[:e].copy(), w[:e].copy(), disc[:nd.value].copy()
+
+    def knn_build_subset(self, tnf, cov, row_ids, k: int, variant: int = VARIANT_RUST, which_mask: int = 3):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        row_ids = np.ascontiguousarray(row_ids, np.uint64)
+        n = (tnf if tnf is not None else cov).shape[0]
+        d = tnf.shape[1] if tnf is not None else NBINS
+        s = cov.shape[1] // 2 if cov is not None else 1
+        m = len(row_ids)
+        ti, td = np.zeros((m, k), np.uint32), np.zeros((m, k), np.float32)
+        di, dd = np.zeros((m, k), np.uint32), np.zeros((m, k), np.float32)
+        self._chk(self.lib.rg_knn_build_subset(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s,
+                                               _lib.ptr(row_ids, C.c_uint64), m, k, variant, which_mask,
+                                               _lib.ptr(ti, C.c_uint32), _lib.ptr(td, C.c_float),
+                                               _lib.ptr(di, C.c_uint32), _lib.ptr(dd, C.c_float)))
+        self._n = m
+        return (ti, td), (di, dd)
+
+    # ------------------------------------------------------------------ one process per GPU (NCCL inside the library)
+    def comm_init(self, rank: int, world: int, uid: np.ndarray):
+        uid = np.ascontiguousarray(uid, np.uint8)
+        assert uid.size == 128
+        self._chk(self.lib.rg_comm_init(self.h, rank, world, _lib.ptr(uid, C.c_uint8)))
+        self.rank, self.world = rank, world
+
+    def comm_destroy(self):
+        self._chk(self.lib.rg_comm_destroy(self.h))
+
+    def knn_load_dist(self, tnf, cov, n: int, d: int, s: int, variant: int = VARIANT_RUST, root: int = 0):
+        """Collective.  Only `root` needs the tables (others may pass None)."""
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        self._n = n
+        self._chk(self.lib.rg_knn_load_dist(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, variant, root))
+
+    def knn_build_dist_dev(self, which: int, k: int, gather: bool, idx_ptr: int, dist_ptr: int):
+        """Collective, asynchronous on self.stream; idx / dist are device arrays [n][k]."""
+        self._chk(self.lib.rg_knn_build_dist_dev(self.h, which, k, int(gather), idx_ptr, dist_ptr))
+
+    def knn_build_dist(self, which: int, k: int, gather: bool = True, out=None):
+        """Collective -> (idx u32 [n,k], dist f32 [n,k]) host arrays; gather=False fills only this rank's rows."""
+        if out is not None:
+            idx, dist = out
+            assert idx.shape == (self._n, k) and idx.dtype == np.uint32 and dist.dtype == np.float32
+        else:
+            idx = np.zeros((self._n, k), np.uint32)
+            dist = np.zeros((self._n, k), np.float32)
+        self._chk(self.lib.rg_knn_build_dist(self.h, which, k, int(gather), _lib.ptr(idx, C.c_uint32), _lib.ptr(dist, C.c_float)))
+        return idx, dist
+
+    def dist_timings(self) -> dict:
+        t = DistTimings()
+        self._chk(self.lib.rg_get_dist_timings(self.h, C.byref(t)))
+        return t.as_dict()
 
     def knn_kprime(self, which: int, k: int) -> int:
         return int(self.lib.rg_knn_kprime(self.h, which, k))
@@ -217,3 +304,71 @@ class Context:
         self._chk(self.lib.rg_graph_intersect(self.h, _lib.ptr(base, C.c_uint32), _lib.ptr(other, C.c_uint32),
                                               base.shape[0], base.shape[1], keep_n_edges, _lib.ptr(keep, C.c_uint8)))
         return keep
+
+
+class Multi:
+    """rg_multi: n GPUs behind one caller thread (one worker thread + one handle per device inside the library)."""
+
+    def __init__(self, devices):
+        self.lib = _lib.load()
+        devs = (C.c_int32 * len(devices))(*devices)
+        m = C.c_void_p()
+        rc = self.lib.rg_multi_create(devs, len(devices), C.byref(m))
+        if rc:
+            raise RosellaGpuError(rc, (self.lib.rg_multi_last_error(None) or b"").decode())
+        self.m = m
+        self.devices = list(devices)
+
+    def close(self):
+        if getattr(self, "m", None):
+            self.lib.rg_multi_destroy(self.m)
+            self.m = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc: int):
+        if rc:
+            raise RosellaGpuError(rc, (self.lib.rg_multi_last_error(self.m) or b"").decode())
+
+    def handle(self, i: int) -> Context:
+        return Context(self.devices[i], _borrowed=self.lib.rg_multi_handle(self.m, i))
+
+    def knn_build(self, tnf, cov, k: int, variant: int = VARIANT_RUST, which_mask: int = 3):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        n = (tnf if tnf is not None else cov).shape[0]
+        d = tnf.shape[1] if tnf is not None else NBINS
+        s = cov.shape[1] // 2 if cov is not None else 1
+        ti, td = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        di, dd = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        self._chk(self.lib.rg_multi_knn_build(self.m, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, k, variant,
+                                              which_mask, _lib.ptr(ti, C.c_uint32), _lib.ptr(td, C.c_float),
+                                              _lib.ptr(di, C.c_uint32), _lib.ptr(dd, C.c_float)))
+        return (ti, td), (di, dd)
+
+    def knn_build_mutual(self, tnf, cov, k: int, keep_n_edges: int, variant: int = VARIANT_RUST):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        n, d, s = tnf.shape[0], tnf.shape[1], cov.shape[1] // 2
+        off = np.zeros(n + 1, np.uint64)
+        nbr, w = np.zeros(n * k, np.uint32), np.zeros(n * k, np.float32)
+        disc, nd = np.zeros(n, np.uint32), C.c_uint64(0)
+        self._chk(self.lib.rg_multi_knn_build_mutual(self.m, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, k,
+                                                     variant, keep_n_edges, _lib.ptr(off, C.c_uint64), _lib.ptr(nbr, C.c_uint32),
+                                                     _lib.ptr(w, C.c_float), C.byref(nd), _lib.ptr(disc, C.c_uint32)))
+        e = int(off[-1])
+        return off, nbr[:e].copy(), w[:e].copy(), disc[:nd.value].copy()
+
+    def tnf_count_ascii(self, seq, offsets):
+        seq = np.ascontiguousarray(seq, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        counts, nk, freqs = np.zeros((n, NBINS), np.uint32), np.zeros(n, np.uint64), np.zeros((n, NBINS), np.float64)
+        self._chk(self.lib.rg_multi_tnf_count_ascii(self.m, _lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n,
+                                                    _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
+                                                    _lib.ptr(freqs, C.c_double)))
+        return counts, nk, freqs
