@@ -54,7 +54,7 @@ typedef enum {
 
 /* which kNN list */
 #define RG_GRAPH_TNF 0u        /* TNFDistance,   embedder.rs:41-48 (tnf_nn) */
-#define RG_GRAPH_DEPTH 1u      /* DepthDistance, embedder.rs:32-39 (depth_nn); MinHash factor = 1 */
+#define RG_GRAPH_DEPTH 1u      /* DepthDistance, embedder.rs:32-39 (depth_nn); MinHash factor: rg_knn_load_sketches */
 #define RG_GRAPH_TNF_EUCLID 2u /* Euclidean distance of the TNF rows as passed: flight's second TNF index,
                                   flight/flight/rosella/embedding.py:163 (metrics.py:64-77); any variant;
                                   a NaN distance (non-finite row) is reported as FLT_MAX */
@@ -116,6 +116,15 @@ int32_t rg_tnf_fetch(rg_handle *h, uint32_t *counts, uint64_t *n_kmers, double *
  * (the reference panics in Normal::new, coverage_calculator.rs:639). */
 int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
                     uint32_t s, uint32_t variant);
+
+/* The MinHash factor of DepthDistance (src/embedding/embedder.rs:133-171): with sketches loaded, RG_GRAPH_DEPTH is
+ *     metabat x (1 - min_jaccard) as f32,   min_jaccard of raw_distance (src/sketch/sketch_distances.rs:61-126),
+ * exactly what DepthDistance::eval returns; without them the factor is 1.  The sketches are the caller's: finch
+ * computes them on the reference side (src/sketch/contig_sketcher.rs:47-92; Sketch.hashes, sorted and unique), row i =
+ * hashes[offsets[i] .. offsets[i+1]), offsets[0] = 0, n = the loaded rows; scale = SketchParams::Scaled.scale (0.1 by
+ * default, 0 = unscaled).  Call after rg_knn_load (a new rg_knn_load drops the sketches).  RG_ERR_INVALID when a list
+ * is not strictly increasing or one hash occurs in more than 4096 sketches. */
+int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, const uint64_t *offsets, uint64_t n, double scale);
 
 /* Exact top-k of query rows [q_begin, q_end) against all n loaded rows, self excluded, ascending
  * by (f32 distance, index).  idx/dist: (q_end-q_begin) x k; rows with fewer than k candidates are
@@ -227,6 +236,20 @@ int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *
                                   uint32_t *neighbours, float *weights, uint64_t *n_disconnected, uint32_t *disconnected);
 int32_t rg_multi_tnf_count_ascii(rg_multi *m, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t *counts,
                                  uint64_t *n_kmers, double *freqs);
+
+/* ------------------------------------------------------------------ flight's all-pairs rank statistic */
+/* ProfileDistanceEngine.makeRankStat (flight/flight/distance.py:92-108, as flight/flight/rosella/rosella.py:337-350
+ * calls it: fun = a / max(a)): for every pair i < j
+ *     stat = (cov_rank / max cov_rank)^w * (kmer_rank / max kmer_rank),   w = max(1/3, s / (s + 4)), 1/2 when s == 1,
+ * cov_rank = fractional rank (ties averaged, distance.py:168-201) of metrics.coverage_distance among all pairs,
+ * kmer_rank = the same for the Euclidean TNF distance with pair weights lengths[i] * lengths[j] (distance.py:53-58).
+ * tnf: n x d rows as flight holds them (clr(x + 1)); cov: n x 2s interleaved mean, var; lengths: contigLen as f64.
+ * Outputs (either may be NULL): stat_condensed, n (n - 1) / 2 values in scipy's pdist order — what the reference
+ * returns; idx / stat_knn, n x k: per row the k pairs with the smallest statistic, ascending by (stat, index) — the
+ * sparse form a kNN consumer needs instead of squareform(stat).  All f64 on the device; n <= 200000 and
+ * 9 x 8 x n (n - 1) / 2 bytes of HBM (RG_ERR_OOM beyond).  Timings: select_ms = distances, rescore_ms = ranks. */
+int32_t rg_rank_stat(rg_handle *h, const double *tnf, const double *cov, const double *lengths, uint64_t n, uint32_t d,
+                     uint32_t s, uint32_t k, double *stat_condensed, uint32_t *idx, double *stat_knn);
 
 /* ------------------------------------------------------------------ graph post-ops */
 /* keep[i*k+j] = 1 when edge j of node i survives mutual_knn / intersect

@@ -20,7 +20,7 @@ TNF, DEPTH, TNF_EUCLID = 0, 1, 2
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_tnf.c", "oracle_metrics.c", "oracle_knn.c", "oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_tnf.c", "oracle_metrics.c", "oracle_knn.c", "oracle_sketch.c", "oracle.h")]
     if force or not os.path.exists(_LIB_PATH) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs
     ):
@@ -38,9 +38,9 @@ def lib() -> C.CDLL:
             build()
         _lib = C.CDLL(_LIB_PATH)
         _lib.orc_normalize.restype = C.c_size_t
-        for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat"):
+        for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat", "orc_min_jaccard"):
             getattr(_lib, f).restype = C.c_double
-        for f in ("orc_tnf_distance_f32", "orc_depth_distance_f32"):
+        for f in ("orc_tnf_distance_f32", "orc_depth_distance_f32", "orc_sketch_distance_f32", "orc_depth_distance_sketch_f32"):
             getattr(_lib, f).restype = C.c_float
     return _lib
 
@@ -167,6 +167,39 @@ def build_mutual_kgraph(depth_idx, depth_dist, tnf_idx, keep_n_edges: int):
     offsets = np.zeros(n + 1, np.uint64)
     offsets[1:] = np.cumsum(counts)
     return offsets, f_idx[keep2], f_dist[keep2], np.where(counts == 0)[0].astype(np.uint32)
+
+
+def min_jaccard(q, r, scale: float = 0.1) -> float:
+    """raw_distance(...).2 of sketch_distances.rs:61-126 for two sorted u64 hash lists."""
+    q = np.ascontiguousarray(q, np.uint64); r = np.ascontiguousarray(r, np.uint64)
+    return lib().orc_min_jaccard(_p(q, C.c_uint64), C.c_uint64(len(q)), _p(r, C.c_uint64), C.c_uint64(len(r)), C.c_double(scale))
+
+
+def depth_distance_sketch(a, b, qa, qb, variant: int = RUST, scale: float = 0.1) -> float:
+    """DepthDistance::eval (embedder.rs:133-171): metabat x (1 - min_jaccard), f32."""
+    a = np.ascontiguousarray(a, np.float64); b = np.ascontiguousarray(b, np.float64)
+    qa = np.ascontiguousarray(qa, np.uint64); qb = np.ascontiguousarray(qb, np.uint64)
+    return lib().orc_depth_distance_sketch_f32(_p(a, C.c_double), _p(b, C.c_double), C.c_uint32(len(a) // 2), C.c_int(variant),
+                                               _p(qa, C.c_uint64), C.c_uint64(len(qa)), _p(qb, C.c_uint64), C.c_uint64(len(qb)),
+                                               C.c_double(scale))
+
+
+def knn_depth_sketch(cov, hashes, offsets, k: int, variant: int = RUST, scale: float = 0.1, qrows=None, threads: int = 0):
+    """Exhaustive exact top-k of the DepthDistance graph with the MinHash factor.  -> (idx u32[nq,k], dist f32[nq,k])"""
+    cov = np.ascontiguousarray(cov, np.float64)
+    hashes = np.ascontiguousarray(hashes, np.uint64); offsets = np.ascontiguousarray(offsets, np.uint64)
+    n, w = cov.shape
+    if qrows is None:
+        nq, qp = n, None
+    else:
+        qrows = np.ascontiguousarray(qrows, np.uint64)
+        nq, qp = len(qrows), _p(qrows, C.c_uint64)
+    idx = np.zeros((nq, k), np.uint32)
+    dist = np.zeros((nq, k), np.float32)
+    lib().orc_knn_depth_sketch(_p(cov, C.c_double), C.c_uint64(n), C.c_uint32(w), C.c_int(variant), _p(hashes, C.c_uint64),
+                               _p(offsets, C.c_uint64), C.c_double(scale), qp, C.c_uint64(nq), C.c_uint32(k),
+                               _p(idx, C.c_uint32), _p(dist, C.c_float), C.c_int(threads))
+    return idx, dist
 
 
 def max_threads() -> int:

@@ -10,6 +10,8 @@
                       no equal-variance sign rule fires this IS MetabatDistance::distance of
                       coverage_calculator.rs:588-666 (epsilon 1e-7 instead of 1e-6) — it pins the RUST variant's main
                       branch on reference-run output (make_rust_pin).
+  flight_rankstat.npz ProfileDistanceEngine.makeRanks / makeRankStat of flight/flight/distance.py:47-108 on seeded inputs
+                      (the default product's O(N^2) rank statistic).
   tnf_fixtures.npz    the reference's bundled FASTA inputs (tests/data/ben/random10000.fna and
                       the first records of 1.fna.gz) as bytes + offsets, with counts produced by
                       a literal pure-Python model of kmer_counting.rs:64-109 written here
@@ -127,6 +129,39 @@ def make_rust_pin(m):
     print("rust_pin.npz:", {k: (v.shape, int(v.sum()) if v.dtype == bool else None) for k, v in out.items()})
 
 
+def make_rankstat():
+    """flight_rankstat.npz: the reference's own ProfileDistanceEngine.makeRankStat (flight/flight/distance.py:92-108:
+    pdist(cov, coverage_distance), pdist(tnf, 'euclidean'), length-weighted fractional ranks :168-201) driven exactly as
+    rosella.py:337-350 drives it (fun = a / max(a), use_multiple_processes=False).  distance.py imports `pebble` (absent
+    here, used only by the multi-process branch), so an empty stand-in module satisfies the import."""
+    import types
+    sys.dont_write_bytecode = True
+    sys.modules.setdefault("pebble", types.ModuleType("pebble"))
+    sys.path.insert(0, f"{REF}/flight")
+    import flight.distance as fd
+    rng = np.random.default_rng(20261106)
+    out = {}
+    for s in (1, 3, 10):
+        n = 90
+        cov = coverage_rows(rng, n, s)
+        cov[7] = cov[8] = cov[9]                   # ties in the coverage distances (coverage_distance == 0, metrics.py:429-431)
+        tnf = rng.dirichlet(8 * np.ones(136), n)
+        x = np.log(rng.multinomial(3000, tnf[0], n) * 0 + np.stack([rng.multinomial(3000, p) for p in tnf]) + 1.0)
+        x -= x.mean(axis=1, keepdims=True)
+        x[11] = x[12]                              # a tie at Euclidean distance 0
+        lengths = np.rint(np.exp(rng.uniform(np.log(2000.0), np.log(500000.0), n))).astype(np.int64)
+        de = fd.ProfileDistanceEngine()
+        from scipy.spatial.distance import pdist
+        out[f"cov_dist_s{s}"] = pdist(cov, fd.metrics.coverage_distance)      # what choose_rank_method ranks (distance.py:127-133)
+        out[f"kmer_dist_s{s}"] = pdist(x, metric="euclidean")
+        cov_ranks, kmer_ranks = de.makeRanks(cov, x, lengths, silent=True, use_multiple_processes=False)
+        stat = de.makeRankStat(cov, x, lengths, silent=True, fun=lambda a: a / max(a), use_multiple_processes=False)
+        out[f"cov_s{s}"], out[f"tnf_s{s}"], out[f"len_s{s}"] = cov, x, lengths
+        out[f"cov_ranks_s{s}"], out[f"kmer_ranks_s{s}"], out[f"stat_s{s}"] = cov_ranks, kmer_ranks, stat
+    np.savez_compressed(os.path.join(OUT, "flight_rankstat.npz"), **out)
+    print("flight_rankstat.npz:", {k: v.shape for k, v in out.items() if k.startswith("stat")})
+
+
 def read_fasta(fh):
     names, seqs, cur = [], [], None
     for line in fh:
@@ -205,3 +240,4 @@ if __name__ == "__main__":
     fm = load_flight_metrics()
     make_flight(fm)
     make_rust_pin(fm)
+    make_rankstat()

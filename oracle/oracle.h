@@ -80,6 +80,19 @@ void orc_mutual_knn(const uint32_t *idx, uint64_t n, uint32_t k, uint32_t keep_n
 void orc_intersect(const uint32_t *base, const uint32_t *other, uint64_t n, uint32_t k,
                    uint32_t keep_n_edges, uint8_t *keep);
 
+/* MinHash factor of DepthDistance (oracle_sketch.c): raw_distance / SketchDistance::eval
+ * (src/sketch/sketch_distances.rs:61-126,:136-154) and DepthDistance::eval (src/embedding/embedder.rs:133-171).
+ * Sketches are sorted u64 hash lists given by the caller (finch computes them on the reference side). */
+double orc_min_jaccard(const uint64_t *q, uint64_t nq, const uint64_t *r, uint64_t nr, double scale);
+float orc_sketch_distance_f32(const uint64_t *q, uint64_t nq, const uint64_t *r, uint64_t nr, double scale);
+float orc_depth_distance_sketch_f32(const double *a, const double *b, uint32_t s, int variant,
+                                    const uint64_t *qa, uint64_t na, const uint64_t *qb, uint64_t nb, double scale);
+void orc_knn_depth_sketch(const double *cov, uint64_t n, uint32_t width, int variant, const uint64_t *hashes,
+                          const uint64_t *offsets, double scale, const uint64_t *qrows, uint64_t nq, uint32_t k,
+                          uint32_t *idx_out, float *dist_out, int threads);
+
+void orc_coverage_distance_condensed(const double *cov, uint64_t n, uint32_t s, double *out, int threads);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -18,10 +18,10 @@ SYMBOLS = [
     "rg_abi_version", "rg_create", "rg_destroy", "rg_last_error", "rg_sync", "rg_stream", "rg_set_option",
     "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
-    "rg_knn_load", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
+    "rg_knn_load", "rg_knn_load_sketches", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
-    "rg_knn_refilter", "rg_knn_build_subset",
+    "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat",
     "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
     "rg_knn_build_dist", "rg_get_dist_timings",
     "rg_multi_create", "rg_multi_destroy", "rg_multi_last_error", "rg_multi_size", "rg_multi_handle", "rg_multi_knn_build",
@@ -85,6 +85,7 @@ def load() -> C.CDLL:
         "rg_tnf_count_resident": (C.c_int32, [vp]),
         "rg_tnf_fetch": (C.c_int32, [vp, u32p, u64p, f64p]),
         "rg_knn_load": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
+        "rg_knn_load_sketches": (C.c_int32, [vp, u64p, u64p, C.c_uint64, C.c_double]),
         "rg_knn_search": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, u32p, f32p, u32p]),
         "rg_knn_search_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, vp, vp, vp]),
         "rg_knn_kprime": (C.c_uint32, [vp, C.c_uint32, C.c_uint32]),
@@ -98,6 +99,7 @@ def load() -> C.CDLL:
         "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
         "rg_knn_flagged_rows": (C.c_int32, [vp, u32p, f32p, f32p, C.c_uint64, C.POINTER(C.c_uint64)]),
+        "rg_rank_stat": (C.c_int32, [vp, f64p, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, f64p, u32p, f64p]),
         "rg_knn_refilter": (C.c_int32, [vp, C.c_uint32, u64p, u32p, f32p, u64p, u32p]),
         "rg_knn_build_subset": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, u64p, C.c_uint64, C.c_uint32,
                                             C.c_uint32, C.c_uint32, u32p, f32p, u32p, f32p]),

@@ -17,11 +17,11 @@ HOST_SOURCES = ["kmer_table.cpp", "fastx.cpp", "embedder.cpp", "capi.cpp"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall", "--expt-relaxed-constexpr"]
 # per-file extra flags: the f64 re-evaluation must not contract a*b+c into FMA (reference op order)
-EXTRA = {"knn_rescore.cu": ["-fmad=false"]}
+EXTRA = {"knn_rescore.cu": ["-fmad=false"], "rank_stat.cu": ["-fmad=false"]}
 SOURCES = ["rg_api.cu", "knn_transform.cu", "knn_depth2.cu", "knn_depth_sym.cu", "knn_tnf.cu", "knn_tnf_tc.cu", "knn_rescore.cu", "knn_exact.cu", "knn_search.cu",
-           "tnf_count.cu", "tnf_count2.cu", "tnf_api.cu", "graph_ops.cu", "rg_comm.cu", "knn_dist.cu", "rg_multi.cu", "tnf_host.cpp"]
+           "tnf_count.cu", "tnf_count2.cu", "tnf_api.cu", "graph_ops.cu", "rg_comm.cu", "knn_dist.cu", "rg_multi.cu", "rank_stat.cu", "tnf_host.cpp"]
 TOOLS = {"microbench.cu": "microbench", "microbench2.cu": "microbench2"}
-HEADERS = ["rg_internal.cuh", "rg_comm.h", "pk.cuh", "knn_tnf_common.cuh", "knn_depth_common.cuh", "tnf_tables.h", os.path.join("..", "..", "include", "rosella_gpu.h")]
+HEADERS = ["rg_internal.cuh", "rg_comm.h", "metric_f64.cuh", "pk.cuh", "knn_tnf_common.cuh", "knn_depth_common.cuh", "tnf_tables.h", os.path.join("..", "..", "include", "rosella_gpu.h")]
 
 
 def _nvcc() -> str:
@@ -67,15 +67,18 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if failed:
         raise RuntimeError("nvcc failed")
     if force or procs or _stale(LIB, objs):
-        cmd = [nvcc, *_host_cxx(), *ARCH, "-shared", "-o", LIB, *objs, "-lpthread", "-ldl"]
+        # link to a temporary name and rename: a reader (a gpurun snapshot, a running test) never sees a half-written .so
+        cmd = [nvcc, *_host_cxx(), *ARCH, "-shared", "-o", LIB + ".tmp", *objs, "-lpthread", "-ldl"]
         subprocess.check_call(cmd)
+        os.replace(LIB + ".tmp", LIB)
     # C++ host mirror of the reference interface (host/rosella_host.hpp), on top of the C ABI
     hsrc = [os.path.join(HOST_DIR, f) for f in HOST_SOURCES]
     hdeps = hsrc + [os.path.join(HOST_DIR, "rosella_host.hpp"), os.path.join(HERE, "..", "include", "rosella_gpu.h"), LIB]
     if force or _stale(HOST_LIB, hdeps):
         subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-std=c++17", "-fPIC",
-                               "-Wall", "-shared", "-o", HOST_LIB, *hsrc, "-L" + HERE, "-lrosella_gpu", "-lz",
+                               "-Wall", "-shared", "-o", HOST_LIB + ".tmp", *hsrc, "-L" + HERE, "-lrosella_gpu", "-lz",
                                "-Wl,-rpath,$ORIGIN"])
+        os.replace(HOST_LIB + ".tmp", HOST_LIB)
     # stand-alone micro-benchmarks (bench.py's live FP32 peak; the issue-model probe)
     for src, exe in TOOLS.items():
         s, e = os.path.join(CSRC, src), os.path.join(OBJ, exe)

@@ -7,120 +7,12 @@
 #include <algorithm>
 
 #include "knn_depth_common.cuh"
+#include "metric_f64.cuh"
 #include "rg_internal.cuh"
 
 namespace {
 
-__device__ double kmer_correlation_f64(const double *__restrict__ x, const double *__restrict__ y, uint32_t d) {
-    double sx = 0.0, sy = 0.0;
-    for (uint32_t j = 0; j < d; ++j) sx += x[j];
-    for (uint32_t j = 0; j < d; ++j) sy += y[j];
-    const double mu_x = sx / (double)d, mu_y = sy / (double)d;          // :367-368
-    double norm_x = 0.0, norm_y = 0.0, dot = 0.0;
-    for (uint32_t j = 0; j < d; ++j) {                                    // :375-381
-        const double a = x[j] - mu_x, b = y[j] - mu_y;
-        dot += a * b;
-        norm_x += a * a;
-        norm_y += b * b;
-    }
-    if (norm_x == 0.0 && norm_y == 0.0) return 0.0;                       // :383
-    if (dot == 0.0) return 1.0;                                           // :385
-    norm_x = norm_x / ((double)d - 1.0);                                  // :401-403
-    norm_y = norm_y / ((double)d - 1.0);
-    dot = dot / ((double)d - 1.0);
-    const double vlr = -2.0 * dot + norm_x + norm_y;                      // :404
-    double rho = 1.0 - vlr / (norm_x + norm_y);                           // :405-408
-    rho += 1.0;
-    rho = 2.0 - rho;
-    rho /= 2.0;
-    if (isnan(rho)) return 1.0;                                           // :410
-    return rho;
-}
-
-__device__ double rho_flight_f64(const double *__restrict__ x, const double *__restrict__ y, uint32_t d) {
-    double mu_x = 0.0, mu_y = 0.0;
-    for (uint32_t j = 0; j < d; ++j) { mu_x += x[j]; mu_y += y[j]; }
-    mu_x /= (double)d;
-    mu_y /= (double)d;
-    double norm_x = 0.0, norm_y = 0.0, dot = 0.0;
-    for (uint32_t j = 0; j < d; ++j) {
-        const double a = x[j] - mu_x, b = y[j] - mu_y;
-        norm_x += a * a;
-        norm_y += b * b;
-        dot += a * b;
-    }
-    norm_x /= (double)(d - 1);
-    norm_y /= (double)(d - 1);
-    dot /= (double)(d - 1);
-    const double vlr = -2.0 * dot + norm_x + norm_y;
-    double rho = 1.0 - vlr / (norm_x + norm_y);
-    rho += 1.0;
-    return 2.0 - rho;
-}
-
-// flight/flight/metrics.py:64-77 (tnf_euclidean)
-__device__ double tnf_euclidean_f64(const double *__restrict__ x, const double *__restrict__ y, uint32_t d) {
-    double r = 0.0;
-    for (uint32_t j = 0; j < d; ++j) r += (x[j] - y[j]) * (x[j] - y[j]);
-    return sqrt(r);
-}
-
-// statrs Normal::cdf (call sites coverage_calculator.rs:647,:650)
-__device__ __forceinline__ double cdf_statrs(double mean, double sd, double x) {
-    return 0.5 * erfc((mean - x) / (sd * 1.4142135623730951));
-}
-// flight/metrics.py:543-558
-__device__ __forceinline__ double cdf_flight(double mean, double sd, double x) {
-    const double y = 0.5 * (1.0 + erf((x - mean) / (sd * sqrt(2.0))));
-    return y > 1.0 ? 1.0 : y;
-}
-
-template <int VARIANT>
-__device__ double metabat_f64(const double *__restrict__ a, const double *__restrict__ b, uint32_t s) {
-    const double EPS = VARIANT == RG_VARIANT_FLIGHT ? 1e-6 : 0.0000001;
-    double lnsum = 0.0;
-    uint32_t cnt = 0;
-    for (uint32_t i = 0; i < s; ++i) {
-        const double a_mean = a[2 * i] + EPS, b_mean = b[2 * i] + EPS;     // :600-603
-        double a_var = a[2 * i + 1] + EPS, b_var = b[2 * i + 1] + EPS;
-        if (a_var < 1.0) a_var = 1.0;                                      // :604-609
-        if (b_var < 1.0) b_var = 1.0;
-        if ((a_mean > EPS || b_mean > EPS) && a_mean != b_mean) {          // :619
-            double k1, k2;
-            if (fabs(a_var - b_var) < 1e-4) {                              // :620
-                k1 = k2 = (a_mean + b_mean) / 2.0;
-            } else {                                                       // :625-627
-                const double tmp = sqrt(a_var * b_var * ((a_mean - b_mean) * (a_mean - b_mean) -
-                                        2.0 * (a_var - b_var) * log(sqrt(b_var / a_var))));
-                k1 = (tmp - a_mean * b_var + b_mean * a_var) / (a_var - b_var);
-                k2 = (tmp + a_mean * b_var - b_mean * a_var) / (b_var - a_var);
-            }
-            if (k1 > k2) { const double t = k1; k1 = k2; k2 = t; }         // :630
-            double m1, s1, m2, s2;
-            if (a_var > b_var) { m1 = b_mean; s1 = sqrt(b_var); m2 = a_mean; s2 = sqrt(a_var); }  // :638-644
-            else               { m1 = a_mean; s1 = sqrt(a_var); m2 = b_mean; s2 = sqrt(b_var); }
-            double dd;
-            if (VARIANT == RG_VARIANT_RUST) {
-                if (fabs(k1 - k2) < EPS) dd = cdf_statrs(m1, s1, k1) - cdf_statrs(m2, s2, k1);     // :646-648
-                else dd = fabs(cdf_statrs(m1, s1, k2) - cdf_statrs(m1, s1, k1) +
-                               cdf_statrs(m2, s2, k1) - cdf_statrs(m2, s2, k2));                   // :650
-            } else {
-                if (k1 == k2) dd = fabs(cdf_flight(m1, s1, k1) - cdf_flight(m2, s2, k1));          // metrics.py:516-519
-                else dd = fabs(cdf_flight(m1, s1, k2) - cdf_flight(m1, s1, k1) +
-                               cdf_flight(m2, s2, k1) - cdf_flight(m2, s2, k2));
-                dd = fmin(fmax(dd, 1e-6), 1.0 - 1e-6);
-            }
-            lnsum += log(dd);
-            cnt += 1;
-        }
-    }
-    if (cnt > 0) {
-        double d = exp(lnsum / (double)cnt);                               // :659
-        if (VARIANT == RG_VARIANT_RUST && isnan(d)) d = 1.0;               // :660
-        return d;
-    }
-    return 1.0;                                                            // :665
-}
+using namespace metric64;
 
 // the f32 distance the boundary reports for the pair (qrow, rrow): the reference's f64 metric truncated to f32 with
 // the NaN guards of embedder.rs:122-125 / :165-170
@@ -140,6 +32,76 @@ __device__ __forceinline__ float pair_distance_f32(const double *__restrict__ qr
     return isnan(v) ? 1.0f : (float)v;                                     // embedder.rs:165-170
 }
 
+// MinHash sketches of the rows (rg_knn_load_sketches); hash == nullptr: no sketches, factor 1
+struct SketchArgs {
+    const uint64_t *hash, *off;
+    uint64_t max_hash;
+};
+
+__device__ __forceinline__ uint64_t sk_lower_bound(const uint64_t *p, uint64_t n, uint64_t key, bool upper) {
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if (p[mid] < key || (upper && p[mid] == key)) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// SketchDistance::eval for one pair (sketch_distances.rs:136-154): (1 - min_jaccard) as f32, NaN -> 1, with
+// min_jaccard = common / min(i, j) of raw_distance (:61-126).  `common` comes from the hash join (knn_exact.cu); i and
+// j are where the reference's merge walk and its scaled tail walk stop: the list that ends first is consumed whole,
+// the other one up to that list's last hash, then both advance over their hashes below max_hash.
+__device__ float sketch_factor(const SketchArgs &sk, uint32_t q, uint32_t j, uint32_t common) {
+    const uint64_t qb = sk.off[q], nq = sk.off[q + 1] - qb, rb = sk.off[j], nr = sk.off[j + 1] - rb;
+    if (common == 0 && nq && nr) return 1.0f;               // 0 / min(i, j), or 0 / 0 = NaN -> 1: the factor is exactly 1
+    const uint64_t *qh = sk.hash + qb, *rh = sk.hash + rb;
+    uint64_t i = 0, jj = 0;
+    if (nq && nr) {
+        const uint64_t ql = qh[nq - 1], rl = rh[nr - 1];
+        if (ql < rl) { i = nq; jj = sk_lower_bound(rh, nr, ql, true); }
+        else if (ql > rl) { jj = nr; i = sk_lower_bound(qh, nq, rl, true); }
+        else { i = nq; jj = nr; }
+    } else {
+        common = 0;
+    }
+    if (sk.max_hash) {                                       // :83-98
+        const uint64_t iq = sk_lower_bound(qh, nq, sk.max_hash, false), ir = sk_lower_bound(rh, nr, sk.max_hash, false);
+        if (iq > i) i = iq;
+        if (ir > jj) jj = ir;
+    }
+    double mj;
+    if (i == 0 && jj == 0) mj = 1.0;                         // :109-111
+    else mj = (double)common / (double)(i < jj ? i : jj);    // :112
+    float res = (float)(1.0 - mj);                           // :143
+    if (isnan(res)) res = 1.0f;                              // :150-152
+    return res;
+}
+
+// DepthDistance::eval for one pair (embedder.rs:133-171) -> the f32 the boundary reports; *metabat32 gets the f32 of
+// the coverage term alone (what the select phase estimated)
+template <int VARIANT>
+__device__ float depth_pair(const double *__restrict__ qrow, const double *__restrict__ rrow, uint32_t width,
+                            const SketchArgs &sk, uint32_t q, uint32_t j, uint32_t common, float *metabat32) {
+    const double m = metabat_f64<VARIANT>(qrow, rrow, width / 2);
+    *metabat32 = isnan(m) ? 1.0f : (float)m;
+    if (!sk.hash) return *metabat32;                         // no sketches: factor 1 (embedder.rs:165-170)
+    const double res = m * (double)sketch_factor(sk, q, j, common);   // :164
+    return isnan(res) ? 1.0f : (float)res;                   // :165-169
+}
+
+// number of sketch hashes rows (grow, j) share: j's entry among the sorted extra candidates of grow
+__device__ __forceinline__ uint32_t common_of(const uint32_t *extra_idx, const uint32_t *extra_common, uint64_t eo, uint32_t cnt,
+                                              uint32_t j, bool *joined) {
+    uint32_t lo = 0, hi = cnt;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (extra_idx[eo + mid] < j) lo = mid + 1; else hi = mid;
+    }
+    const bool hit = lo < cnt && extra_idx[eo + lo] == j;
+    if (joined) *joined = hit;
+    return hit && extra_common ? extra_common[eo + lo] : 0u;
+}
+
 struct RescoreArgs {
     const double *data;            // f64 table of the graph, row-major [n][width]
     uint32_t n, width;
@@ -148,6 +110,8 @@ struct RescoreArgs {
     uint32_t kprime, k, q_begin, q_count;
     const uint64_t *extra_off;     // CSR of extra candidates by GLOBAL row (null: none)
     const uint32_t *extra_idx;
+    const uint32_t *extra_common;  // shared sketch hashes per extra candidate
+    SketchArgs sk;
     const uint8_t *row_flag;       // rows that always take the exhaustive pass (null: none)
     uint32_t ecap;                 // extra candidates evaluated per row at most
     uint32_t *idx_out;
@@ -179,12 +143,13 @@ rescore_kernel(const RescoreArgs a) {
     const uint32_t grow = a.q_begin + q, kprime = a.kprime, k = a.k, n = a.n;
     const double *qrow = a.data + (uint64_t)grow * a.width;
     bool force = a.row_flag && a.row_flag[grow];
-    uint32_t ne = 0;
+    uint32_t ne = 0, ne_all = 0;
     uint64_t eo = 0;
     if (a.extra_off) {
         eo = a.extra_off[grow];
         const uint64_t cnt = a.extra_off[grow + 1] - eo;
         if (cnt > a.ecap) force = true;
+        ne_all = (uint32_t)cnt;
         ne = (uint32_t)(cnt > a.ecap ? a.ecap : cnt);
     }
     const uint32_t total = kprime + ne;
@@ -202,7 +167,15 @@ rescore_kernel(const RescoreArgs a) {
         const uint32_t j = si[e];
         float df = INFINITY;
         if (j < n) {
-            df = pair_distance_f32<VARIANT, WHICH>(qrow, a.data + (uint64_t)j * a.width, a.width);
+            float dm;                                            // what the select phase estimated: the metric without
+            if (WHICH == RG_GRAPH_DEPTH) {                       // the MinHash factor
+                const uint32_t common = !a.sk.hash ? 0u
+                                        : e >= kprime ? a.extra_common[eo + (e - kprime)]
+                                                      : common_of(a.extra_idx, a.extra_common, eo, ne_all, j, nullptr);
+                df = depth_pair<VARIANT>(qrow, a.data + (uint64_t)j * a.width, a.width, a.sk, grow, j, common, &dm);
+            } else {
+                df = dm = pair_distance_f32<VARIANT, WHICH>(qrow, a.data + (uint64_t)j * a.width, a.width);
+            }
             if (e < kprime) {
                 float ds = a.cand_d[(uint64_t)q * kprime + e];
                 if (WHICH == RG_GRAPH_TNF_EUCLID) ds = sqrtf(ds);
@@ -210,8 +183,8 @@ rescore_kernel(const RescoreArgs a) {
                 // (d_select = 0), and a tiny negative equal-variance term is NaN -> 1.0 in f64 (:647,:659-661) where FP32
                 // sees -0 or a positive rounding.  Both only cost a candidate slot; counting them would flag ~1.5 % of
                 // all rows for nothing (profiles/r2b_flags_1m.json).
-                const bool structural = ds == 0.f || (WHICH == RG_GRAPH_DEPTH && df == 1.0f && ds < 1.0f);
-                if (ds < 1e37f && df < 1e37f && !structural) eps = fmaxf(eps, fabsf(ds - df));
+                const bool structural = ds == 0.f || (WHICH == RG_GRAPH_DEPTH && dm == 1.0f && ds < 1.0f);
+                if (ds < 1e37f && dm < 1e37f && !structural) eps = fmaxf(eps, fabsf(ds - dm));
             }
         }
         sd[e] = df;
@@ -288,6 +261,8 @@ struct ExactArgs {
     const float4 *cov_t;           // FP32 operand tiles of the coverage graph (null: TNF graphs)
     const uint64_t *extra_off;
     const uint32_t *extra_idx;
+    const uint32_t *extra_common;
+    SketchArgs sk;
     float *part_d;                 // scratch [gridDim.x][K]: sorted partial lists of split rows
     uint32_t *part_i;
     uint32_t *part_done;           // [gridDim.x] arrival counters of split rows (zero at launch)
@@ -337,8 +312,8 @@ exact_rows_kernel(const ExactArgs a) {
             const float dk = a.flag_dk[f], eps = a.flag_eps[f];
             bound = dk + fmaxf(16.f * eps, 0.25f * fabsf(dk) + 1e-4f);
             if (!(bound < INFINITY)) prefilter = false;
-            if (a.extra_off) { eo = a.extra_off[grow]; ne = (uint32_t)(a.extra_off[grow + 1] - eo); }
         }
+        if (WHICH == RG_GRAPH_DEPTH && a.extra_off) { eo = a.extra_off[grow]; ne = (uint32_t)(a.extra_off[grow + 1] - eo); }
         __syncthreads();
         for (uint32_t c = threadIdx.x; c < width; c += XW * 32) qs[c] = a.data[(uint64_t)grow * width + c];
         for (int e = lane; e < K; e += 32) { ld[warp * K + e] = INFINITY; li[warp * K + e] = 0xffffffffu; }
@@ -365,16 +340,21 @@ exact_rows_kernel(const ExactArgs a) {
                 }
                 const float d32 = depthk::depth_finish<VARIANT>(acc0, cnt0);
                 if (want && d32 > bound) {                 // not a neighbour by the FP32 value: keep only extra candidates
-                    uint32_t lo = 0, hi = ne;
-                    while (lo < hi) {
-                        const uint32_t mid = (lo + hi) >> 1;
-                        if (a.extra_idx[eo + mid] < j) lo = mid + 1; else hi = mid;
-                    }
-                    want = lo < ne && a.extra_idx[eo + lo] == j;
+                    bool joined;
+                    common_of(a.extra_idx, nullptr, eo, ne, j, &joined);
+                    want = joined;
                 }
             }
             float d = INFINITY;
-            if (want) d = pair_distance_f32<VARIANT, WHICH>(qs, a.data + (uint64_t)j * width, width);
+            if (want) {
+                if (WHICH == RG_GRAPH_DEPTH) {
+                    float dm;
+                    const uint32_t common = a.sk.hash ? common_of(a.extra_idx, a.extra_common, eo, ne, j, nullptr) : 0u;
+                    d = depth_pair<VARIANT>(qs, a.data + (uint64_t)j * width, width, a.sk, grow, j, common, &dm);
+                } else {
+                    d = pair_distance_f32<VARIANT, WHICH>(qs, a.data + (uint64_t)j * width, width);
+                }
+            }
             topk_offer<K>(ld + warp * K, li + warp * K, d, j, thr, lane);
         }
         if (threadIdx.x == 0) { s_found = 0; s_last = parts == 1; }
@@ -457,7 +437,12 @@ int32_t launch_exact(rg_handle *h, const double *data, uint32_t width, uint32_t 
     a.idx_out = idx; a.dist_out = dist; a.n_valid = nv;
     if (depth) {
         a.cov_t = (const float4 *)h->cov_t.p;
-        if (h->has_extra) { a.extra_off = (const uint64_t *)h->extra_off.p; a.extra_idx = (const uint32_t *)h->extra_idx.p; }
+        if (h->has_extra) {
+            a.extra_off = (const uint64_t *)h->extra_off.p;
+            a.extra_idx = (const uint32_t *)h->extra_idx.p;
+            a.extra_common = (const uint32_t *)h->extra_common.p;
+        }
+        if (h->has_sketch) a.sk = SketchArgs{(const uint64_t *)h->sk_hash.p, (const uint64_t *)h->sk_off.p, h->sk_max_hash};
     }
     auto go = [&](auto kern) -> int32_t {
         RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -489,7 +474,9 @@ int32_t launch_rescore(rg_handle *h, const double *data, uint32_t width, uint32_
     if (extras) {
         a.extra_off = (const uint64_t *)h->extra_off.p;
         a.extra_idx = (const uint32_t *)h->extra_idx.p;
+        a.extra_common = (const uint32_t *)h->extra_common.p;
         a.row_flag = (const uint8_t *)h->row_flag.p;
+        if (h->has_sketch) a.sk = SketchArgs{(const uint64_t *)h->sk_hash.p, (const uint64_t *)h->sk_off.p, h->sk_max_hash};
     }
     a.idx_out = idx; a.dist_out = dist; a.n_valid = nv;
     if (certify) {

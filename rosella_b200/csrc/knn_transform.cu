@@ -189,7 +189,10 @@ int32_t rg_knn_load_finish(rg_handle *h, bool has_tnf, bool has_cov, uint64_t n,
                        "rg_knn_load: coverage table holds a negative mean (coverage is a read depth; the select phase "
                        "relies on mean + eps >= eps for coverage_calculator.rs:619)");
     h->has_extra = false;
+    h->has_sketch = false;
     h->n_extra = 0;
+    h->n_coll_pairs = 0;
+    h->pending_n = n;
     h->tnf_t_valid = false;
     if (h->cert_ctr.p) RG_CUDA(h, cudaMemsetAsync(h->cert_ctr.p, 0, 8 * sizeof(uint32_t), h->stream));
     if (has_cov && h->opt_certify) {

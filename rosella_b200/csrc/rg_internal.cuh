@@ -55,8 +55,18 @@ struct rg_handle {
     DevBuf row_flag;          // u8 [n]: 1 = this row always takes the exhaustive f64 pass (dense FP32 collision group)
     DevBuf extra_off;         // u64 [n+1] CSR of the extra candidates of each row ...
     DevBuf extra_idx;         // u32 [...]: rows whose FP32 mean / variance collides with the row's while the f64 values differ
+    DevBuf extra_common;      // u32 [...]: number of sketch hashes the pair shares (0: FP32-collision pair only)
     uint64_t n_extra = 0;     // directed extra candidate pairs found by the last load
     bool has_extra = false;
+    DevBuf ws[16];            // load-time scratch of the collision scan / extras rebuild, kept between loads
+    DevBuf coll_pairs;        // u64 [...]: FP32-collision pairs of the last load (row << 32 | row), unsorted
+    uint64_t n_coll_pairs = 0;
+    uint64_t pending_n = 0;   // rows of the load in progress (h->n is published at its end)
+    // ---- MinHash sketches (rg_knn_load_sketches): the (1 - min_jaccard) factor of DepthDistance
+    DevBuf sk_hash, sk_off;   // u64 concatenated sorted hash lists, u64 [n+1] offsets
+    double sk_scale = 0.0;
+    uint64_t sk_max_hash = 0;
+    bool has_sketch = false;
 
     // ---- multi-GPU (rg_comm.cu, knn_dist.cu): one handle = one rank of an NCCL communicator
     void *comm = nullptr;             // ncclComm_t (NCCL is dlopen'ed on first use; single-GPU callers never need it)

@@ -160,6 +160,13 @@ class Context:
         self._n = n
         self._chk(self.lib.rg_knn_load(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, variant))
 
+    def knn_load_sketches(self, hashes, offsets, scale: float = 0.1):
+        """MinHash sketches of the loaded rows (sorted u64 hash lists) -> RG_GRAPH_DEPTH becomes DepthDistance."""
+        hashes = np.ascontiguousarray(hashes, np.uint64)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        self._chk(self.lib.rg_knn_load_sketches(self.h, _lib.ptr(hashes, C.c_uint64), _lib.ptr(offsets, C.c_uint64),
+                                                len(offsets) - 1, scale))
+
     def knn_search(self, which: int, k: int, q_begin: int = 0, q_end: int | None = None):
         q_end = self._n if q_end is None else q_end
         nq = max(q_end - q_begin, 0)
@@ -288,6 +295,18 @@ class Context:
                                                _lib.ptr(eps, C.c_float), cap, C.byref(cnt)))
         m = min(cnt.value, cap)
         return rows[:m] & 0x7FFFFFFF, (rows[:m] >> 31).astype(bool), dk[:m], eps[:m]
+
+    def rank_stat(self, tnf, cov, lengths, k: int = 0, condensed: bool = True):
+        """flight's makeRankStat on the device -> (stat condensed f64 or None, idx u32 [n,k] or None, stat_knn f64 [n,k] or None)"""
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        lengths = np.ascontiguousarray(lengths, np.float64)
+        n, d, s = tnf.shape[0], tnf.shape[1], cov.shape[1] // 2
+        stat = np.zeros(n * (n - 1) // 2, np.float64) if condensed else None
+        idx = np.zeros((n, k), np.uint32) if k else None
+        sk = np.zeros((n, k), np.float64) if k else None
+        self._chk(self.lib.rg_rank_stat(self.h, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), _lib.ptr(lengths, C.c_double),
+                                        n, d, s, k, _lib.ptr(stat, C.c_double), _lib.ptr(idx, C.c_uint32), _lib.ptr(sk, C.c_double)))
+        return stat, idx, sk
 
     # ------------------------------------------------------------------ graph post-ops
     def graph_mutual(self, idx, keep_n_edges: int):

@@ -112,3 +112,33 @@ def fasta_wrap(seq: np.ndarray, offsets: np.ndarray, width: int = 60):
         out.append(buf)
         offs.append(offs[-1] + len(buf))
     return (np.concatenate(out) if out else np.zeros(0, np.uint8)), np.array(offs, np.uint64)
+
+
+MAX_HASH_SCALE_0_1 = (2 ** 64 - 1) // 10      # finch's max_hash for scale 0.1: u64::MAX / (1/scale) as u64
+
+
+def sketches(n: int, seed: int = SEED_KNN + 7, mean_size: int = 60, share_frac: float = 0.05, empty_frac: float = 0.002):
+    """Synthetic scaled MinHash sketches (what finch hands to SketchDistance, src/sketch/contig_sketcher.rs:47-92):
+    per contig a sorted list of distinct u64 hashes, most of them below max_hash(scale = 0.1), a few above (finch pads
+    a scaled sketch up to kmers_to_sketch).  A fraction of the contigs copy part of another contig's hashes (shared
+    31-mers: repeats, overlapping contig ends), a few sketches are empty.  -> (hashes u64[...], offsets u64[n+1])"""
+    rng = np.random.default_rng(seed)
+    sizes = rng.poisson(mean_size, n).astype(np.int64)
+    sizes[rng.random(n) < empty_frac] = 0
+    lists = []
+    for i in range(n):
+        h = rng.integers(0, MAX_HASH_SCALE_0_1, sizes[i], dtype=np.uint64)
+        if sizes[i] and rng.random() < 0.1:                          # padded beyond max_hash
+            h = np.concatenate([h, rng.integers(MAX_HASH_SCALE_0_1, 2 ** 63, 3, dtype=np.uint64)])
+        lists.append(h)
+    donors = rng.integers(0, n, n)
+    for i in np.where(rng.random(n) < share_frac)[0]:
+        d = lists[donors[i]]
+        if len(d) and donors[i] != i:
+            take = d[rng.random(len(d)) < rng.uniform(0.05, 0.9)]
+            lists[i] = np.concatenate([lists[i], take])
+    lists = [np.unique(h) for h in lists]
+    offsets = np.zeros(n + 1, np.uint64)
+    offsets[1:] = np.cumsum([len(h) for h in lists])
+    hashes = np.concatenate(lists) if n else np.zeros(0, np.uint64)
+    return hashes.astype(np.uint64), offsets

@@ -425,3 +425,53 @@ def test_negative_mean_is_rejected(ctx):
     cov[5, 2] = -0.5
     with pytest.raises(gpu.RosellaGpuError, match="negative mean"):
         ctx.knn_load(None, cov)
+
+
+def test_depth_graph_with_the_minhash_factor(ctx):
+    """DepthDistance::eval (embedder.rs:133-171) = metabat x (1 - min_jaccard): with sketches loaded the coverage graph
+    must equal the oracle's exhaustive kNN of the PRODUCT metric — pairs that share hashes move up (or to distance 0 for
+    identical sketches), pairs of empty sketches sit at distance 0 (sketch_distances.rs:109-111), everything else is
+    unchanged — through the batch kernel, the symmetric build and a query sub-range."""
+    n, s, k = 3000, 4, 30
+    _, cov, _ = synth.knn_tables(n, s, seed=61)
+    hashes, offs = synth.sketches(n, seed=9, mean_size=40, share_frac=0.25, empty_frac=0.004)
+    lists = [hashes[int(offs[i]):int(offs[i + 1])] for i in range(n)]
+    ctx.knn_load(None, cov, gpu.VARIANT_RUST)
+    plain_i, plain_d, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    ctx.knn_load_sketches(hashes, offs, 0.1)
+    assert ctx.timings()["extra_pairs"] > 500
+    di, dd, nv = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    oi, od = oracle.knn_depth_sketch(cov, hashes, offs, k, oracle.RUST, 0.1)
+    assert (nv == k).all() and (np.diff(dd, axis=1) >= 0).all()
+    assert (di != plain_i).any(axis=1).sum() > 100            # the factor does change the graph
+    changed = 0
+    for r in range(n):
+        if np.array_equal(di[r], oi[r]):
+            assert np.all(np.abs(dd[r] - od[r]) <= TAU_REL * np.abs(od[r]) + 1e-15)
+            continue
+        changed += 1
+        kth = od[r, -1]
+        got = set(di[r].tolist())
+        for p in range(k):                                     # tie-aware: every oracle neighbour is present or ties the k-th
+            assert int(oi[r, p]) in got or od[r, p] >= kth * (1 - TAU_REL), (r, p)
+        for p in range(k):                                     # and every reported distance is the product metric's
+            want = oracle.depth_distance_sketch(cov[r], cov[di[r, p]], lists[r], lists[di[r, p]], oracle.RUST, 0.1)
+            assert abs(want - dd[r, p]) <= TAU_REL * abs(want) + 1e-15
+    assert changed < 0.01 * n
+    empty = np.where(np.diff(offs.astype(np.int64)) == 0)[0]
+    assert len(empty) >= 2 and dd[empty[0], 0] == 0.0 and di[empty[0], 0] in empty
+    try:                                                       # symmetric block build and a sub-range: same lists
+        ctx.set_option("depth_build", 2); ctx.set_option("sym_block", 512); ctx.set_option("sym_chunk", 1024)
+        si, sd, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    finally:
+        for key in ("depth_build", "sym_block", "sym_chunk"):
+            ctx.set_option(key, 0)
+    assert np.array_equal(si, di) and np.array_equal(sd, dd)
+    pi, pd_, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k, 1000, 1700)
+    assert np.array_equal(pi, di[1000:1700]) and np.array_equal(pd_, dd[1000:1700])
+    ctx.knn_load(None, cov, gpu.VARIANT_RUST)                 # a new load drops the sketches
+    again_i, again_d, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+    assert np.array_equal(again_i, plain_i) and np.array_equal(again_d, plain_d)
+    bad = hashes.copy(); bad[1], bad[0] = bad[0], bad[1]
+    with pytest.raises(gpu.RosellaGpuError, match="strictly increasing"):
+        ctx.knn_load_sketches(bad, offs, 0.1)

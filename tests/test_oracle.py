@@ -161,3 +161,65 @@ def test_metabat_rust_variant_main_branch_is_pinned(golden_dir, s):
     eq = noclamp & ~noneq
     same = np.isclose(got[eq], ref[eq], rtol=1e-9, atol=0)
     assert (same | (got[eq] == 1.0)).all() and same.any() and (~same).any()
+
+
+def _raw_distance_model(q, r, scale):
+    """Literal walk of raw_distance (src/sketch/sketch_distances.rs:61-126) on Python ints."""
+    i = j = common = 0
+    while i < len(q) and j < len(r):
+        if q[i] < r[j]: i += 1
+        elif q[i] > r[j]: j += 1
+        else: common += 1; i += 1; j += 1
+    if scale > 0:
+        max_hash = (2 ** 64 - 1) // int(1.0 / scale)
+        while i < len(q) and q[i] < max_hash: i += 1
+        while j < len(r) and r[j] < max_hash: j += 1
+    if i == 0 and j == 0:
+        return 1.0
+    return common / min(i, j) if min(i, j) else float("nan")
+
+
+def test_min_jaccard_restatement_matches_the_literal_walk():
+    from rosella_b200 import synth
+    hashes, offs = synth.sketches(300, seed=11, mean_size=25, share_frac=0.3, empty_frac=0.03)
+    lists = [[int(x) for x in hashes[int(offs[i]):int(offs[i + 1])]] for i in range(300)]
+    rng = np.random.default_rng(0)
+    seen_shared = seen_nan = seen_tail = 0
+    for a, b in rng.integers(0, 300, (4000, 2)):
+        want = _raw_distance_model(lists[a], lists[b], 0.1)
+        got = oracle.min_jaccard(lists[a], lists[b], 0.1)
+        assert (np.isnan(want) and np.isnan(got)) or got == want
+        seen_shared += 0 < want < 1 if want == want else 0
+        seen_nan += want != want
+        seen_tail += any(x >= synth.MAX_HASH_SCALE_0_1 for x in lists[a] + lists[b])
+    assert seen_shared > 10 and seen_nan > 5 and seen_tail > 50
+    assert oracle.min_jaccard([], [], 0.1) == 1.0                       # :109-111
+    # DepthDistance::eval (embedder.rs:133-171): metabat x (1 - min_jaccard) as f32, NaN -> 1
+    cov = np.array([[5.0, 9.0, 2.0, 3.0], [7.0, 12.0, 0.0, 0.0]])
+    m = oracle.metabat(cov[0], cov[1], oracle.RUST)
+    assert oracle.depth_distance_sketch(cov[0], cov[1], [1, 2, 3, 4], [2, 4, 9], oracle.RUST) == np.float32(m * float(np.float32(1 - 2 / 3)))
+    assert oracle.depth_distance_sketch(cov[0], cov[1], [1, 2], [7, 8], oracle.RUST) == np.float32(m)
+    assert oracle.depth_distance_sketch(cov[0], cov[1], [], [7, 8], oracle.RUST) == np.float32(m)      # NaN -> factor 1
+    assert oracle.depth_distance_sketch(cov[0], cov[1], [], [], oracle.RUST) == 0.0                   # both empty: min_jaccard = 1
+
+
+@pytest.mark.parametrize("s", [1, 3, 10])
+def test_rank_statistic_restatement_is_pinned(golden_dir, s):
+    """oracle/rankstat.py against ProfileDistanceEngine.makeRanks / makeRankStat run from the reference itself
+    (flight/flight/distance.py:47-108; oracle/make_golden.py: make_rankstat).  The rank step is pinned EXACTLY on the
+    reference's own distance vectors; the distances agree to 1e-12.  Ranks computed from the oracle's distances can differ
+    from the reference's where numba's fastmath code returns d(a, b) != d(b, a) in the last bit: with one sample, the
+    pairs (present row, any absent row) tie exactly here and only almost there, so a tie group is averaged differently."""
+    from oracle import rankstat
+    g = np.load(os.path.join(golden_dir, "flight_rankstat.npz"))
+    cov, tnf, lengths = g[f"cov_s{s}"], g[f"tnf_s{s}"], g[f"len_s{s}"]
+    cr, kr, st = rankstat.stat_from_distances(g[f"cov_dist_s{s}"], g[f"kmer_dist_s{s}"], lengths, s)
+    assert np.array_equal(cr, g[f"cov_ranks_s{s}"]) and np.array_equal(kr, g[f"kmer_ranks_s{s}"])
+    assert np.allclose(st, g[f"stat_s{s}"], rtol=1e-14, atol=0)
+    assert len(np.unique(cr)) < len(cr)                  # the fixture holds tied coverage distances
+    dc, dk = rankstat.distances(cov, tnf)
+    assert np.allclose(dc, g[f"cov_dist_s{s}"], rtol=1e-12, atol=0) and np.allclose(dk, g[f"kmer_dist_s{s}"], rtol=1e-13, atol=1e-15)
+    cr2, kr2, st2 = rankstat.rank_stat(cov, tnf, lengths)
+    groups = np.unique(g[f"cov_dist_s{s}"].round(12), return_counts=True)[1]
+    assert np.abs(cr2 - cr).max() <= groups[groups < 300].max() and np.array_equal(kr2, kr)
+    assert np.median(np.abs(st2 - st) / st) < 1e-12
