@@ -258,8 +258,10 @@ def parity_sample(ctx, tnf, cov, k, lists, oracle_rows=64, bit_rows=4096, seed=3
     where two neighbours tie within 2 f32 ulps), and `bit_rows` contiguous rows bit-compared with rg_knn_search through
     the batch kernel (a different select path: no symmetry, no exchange)."""
     import oracle
+    from benchmarks import cpu_arm
     from rosella_b200 import gpu
     n = tnf.shape[0]
+    threads = cpu_arm.host_threads()         # not OMP_NUM_THREADS: torch.distributed.run sets it to 1 for every rank
     rng = np.random.default_rng(seed)
     rows = np.sort(rng.choice(n, min(oracle_rows, n), replace=False)).astype(np.uint64)
     out = {"oracle_rows": int(len(rows)), "bit_rows": 0, "graphs": {}}
@@ -270,7 +272,7 @@ def parity_sample(ctx, tnf, cov, k, lists, oracle_rows=64, bit_rows=4096, seed=3
     ok = True
     for name, which, ow, data in (("depth", gpu.GRAPH_DEPTH, oracle.DEPTH, cov), ("tnf", gpu.GRAPH_TNF, oracle.TNF, tnf)):
         idx, dst = lists[name]
-        oi, od, _ = oracle.knn(data, ow, k, oracle.RUST, qrows=rows)
+        oi, od, _ = oracle.knn(data, ow, k, oracle.RUST, qrows=rows, threads=threads)
         gi, gd = idx[rows], dst[rows]
         hits = total = 0
         max_rel = 0.0
@@ -292,6 +294,7 @@ def parity_sample(ctx, tnf, cov, k, lists, oracle_rows=64, bit_rows=4096, seed=3
         ok &= g["recall"] == 1.0 and bit and max_rel <= 2.4e-7
         out["graphs"][name] = g
     out["ok"] = bool(ok)
+    out["oracle_threads"] = threads
     out["seconds"] = time.perf_counter() - t0
     out["recall"] = min(g["recall"] for g in out["graphs"].values())
     return out

@@ -216,7 +216,8 @@ typedef struct {
     double finish_ms;       /* merge + f64 re-evaluation + certificate (TNF graphs: select + re-evaluation) */
     double gather_ms;       /* all-gather of the finished slabs / device->host copy of this rank's slab */
 } rg_dist_timings;
-int32_t rg_get_dist_timings(rg_handle *h, rg_dist_timings *out);
+int32_t rg_get_dist_timings(rg_handle *h, rg_dist_timings *out);                      /* the last build */
+int32_t rg_get_dist_timings_of(rg_handle *h, uint32_t which, rg_dist_timings *out);    /* the last build of graph `which` */
 
 /* (b) One process, one caller thread, n_dev GPUs: one worker thread and one handle per device inside the library,
  * communicator made with ncclCommInitAll.  The calls mirror the single-GPU ones and return the same results;

@@ -23,7 +23,7 @@ SYMBOLS = [
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
     "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat",
     "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
-    "rg_knn_build_dist", "rg_get_dist_timings",
+    "rg_knn_build_dist", "rg_get_dist_timings", "rg_get_dist_timings_of",
     "rg_multi_create", "rg_multi_destroy", "rg_multi_last_error", "rg_multi_size", "rg_multi_handle", "rg_multi_knn_build",
     "rg_multi_knn_build_mutual", "rg_multi_tnf_count_ascii",
 ]
@@ -60,6 +60,13 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
+    # The library dlopens NCCL on first multi-GPU use and takes a copy the process already holds.  PyTorch bundles its own
+    # libnccl.so.2 (newer than the system's) and must see that one: import torch first when it is installed, so that the
+    # harness, the tests and bench.py never end up with two NCCL versions fighting over one SONAME.
+    try:
+        import torch  # noqa: F401
+    except ImportError:
+        pass
     if not os.path.exists(LIB_PATH):
         raise ImportError(
             f"{LIB_PATH} is missing: build it with `python -m rosella_b200.build` "
@@ -111,6 +118,7 @@ def load() -> C.CDLL:
         "rg_knn_build_dist_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp]),
         "rg_knn_build_dist": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint32, u32p, f32p]),
         "rg_get_dist_timings": (C.c_int32, [vp, C.POINTER(DistTimings)]),
+        "rg_get_dist_timings_of": (C.c_int32, [vp, C.c_uint32, C.POINTER(DistTimings)]),
         "rg_multi_create": (C.c_int32, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]),
         "rg_multi_destroy": (None, [vp]),
         "rg_multi_last_error": (C.c_char_p, [vp]),

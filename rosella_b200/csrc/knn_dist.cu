@@ -44,6 +44,20 @@ int32_t all_gather_rows(rg_handle *h, const NcclApi *api, void *buf, uint64_t n,
 
 }  // namespace
 
+static int32_t resolve_dist_timings(rg_handle *h) {
+    if (h->dtm.partial_ms < 0.0) {
+        const bool with_d2h = h->dtm.partial_ms < -1.5;
+        RG_CUDA(h, cudaSetDevice(h->device));
+        RG_CUDA(h, cudaEventSynchronize(h->dist_ev[with_d2h ? 5 : 4]));
+        h->dtm.partial_ms = rg_elapsed(h->dist_ev[0], h->dist_ev[1]);
+        h->dtm.exchange_ms = rg_elapsed(h->dist_ev[1], h->dist_ev[2]);
+        h->dtm.finish_ms = rg_elapsed(h->dist_ev[2], h->dist_ev[3]);
+        h->dtm.gather_ms = rg_elapsed(h->dist_ev[3], h->dist_ev[with_d2h ? 5 : 4]);
+        if (h->dtm_which <= RG_GRAPH_TNF_EUCLID) h->dtm_graph[h->dtm_which] = h->dtm;
+    }
+    return RG_OK;
+}
+
 extern "C" {
 
 int32_t rg_knn_load_dist(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
@@ -87,6 +101,8 @@ int32_t rg_knn_load_dist(rg_handle *h, const double *tnf, const double *cov, uin
 int32_t rg_knn_build_dist_dev(rg_handle *h, uint32_t which, uint32_t k, uint32_t gather, uint32_t *idx_dev, float *dist_dev) {
     if (!h) return RG_ERR_INVALID;
     if (!idx_dev || !dist_dev) return rg_fail(h, RG_ERR_INVALID, "rg_knn_build_dist: output pointer is NULL");
+    if (h->dist_ev[0]) resolve_dist_timings(h);      // keep the phases of the previous graph (rg_get_dist_timings_of)
+    h->dtm_which = which;
     if (h->world <= 1 || !h->comm) {
         RG_TRY(ensure_events(h));
         RG_CUDA(h, cudaEventRecord(h->dist_ev[0], h->stream));
@@ -181,16 +197,15 @@ int32_t rg_knn_build_dist(rg_handle *h, uint32_t which, uint32_t k, uint32_t gat
 
 int32_t rg_get_dist_timings(rg_handle *h, rg_dist_timings *out) {
     if (!h || !out) return RG_ERR_INVALID;
-    if (h->dtm.partial_ms < 0.0) {
-        const bool with_d2h = h->dtm.partial_ms < -1.5;
-        RG_CUDA(h, cudaSetDevice(h->device));
-        RG_CUDA(h, cudaEventSynchronize(h->dist_ev[with_d2h ? 5 : 4]));
-        h->dtm.partial_ms = rg_elapsed(h->dist_ev[0], h->dist_ev[1]);
-        h->dtm.exchange_ms = rg_elapsed(h->dist_ev[1], h->dist_ev[2]);
-        h->dtm.finish_ms = rg_elapsed(h->dist_ev[2], h->dist_ev[3]);
-        h->dtm.gather_ms = rg_elapsed(h->dist_ev[3], h->dist_ev[with_d2h ? 5 : 4]);
-    }
+    RG_TRY(resolve_dist_timings(h));
     *out = h->dtm;
+    return RG_OK;
+}
+
+int32_t rg_get_dist_timings_of(rg_handle *h, uint32_t which, rg_dist_timings *out) {
+    if (!h || !out || which > RG_GRAPH_TNF_EUCLID) return RG_ERR_INVALID;
+    RG_TRY(resolve_dist_timings(h));
+    *out = h->dtm_graph[which];
     return RG_OK;
 }
 

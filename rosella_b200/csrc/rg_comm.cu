@@ -16,10 +16,16 @@ std::once_flag g_once;
 std::string g_load_error;
 
 void load_nccl() {
+    // a copy the process already holds wins (PyTorch ships its own libnccl.so.2 and needs exactly that version; loading
+    // the system copy first would shadow it for the rest of the process), then the loader's search path
     void *lib = nullptr;
     for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
-        lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+        lib = dlopen(name, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
         if (lib) break;
+    }
+    for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
+        if (lib) break;
+        lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
     }
     if (!lib) {
         g_load_error = std::string("dlopen(libnccl.so.2) failed: ") + dlerror();

@@ -75,7 +75,9 @@ struct rg_handle {
     DevBuf dist_rd, dist_ri;          // all ranks' partial lists of this rank's rows [world][rows][K']
     DevBuf dist_status;               // i32 status word agreed on before a collective is entered
     cudaEvent_t dist_ev[8] = {};
-    rg_dist_timings dtm = {};
+    rg_dist_timings dtm = {};         // last build
+    rg_dist_timings dtm_graph[3] = {};   // last build of each graph
+    uint32_t dtm_which = 0;
 
     // ---- kNN lists kept for rg_knn_refilter (graph_ops.cu)
     DevBuf cache_di, cache_dd, cache_ti, cache_td;

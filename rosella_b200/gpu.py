@@ -255,9 +255,13 @@ class Context:
         self._chk(self.lib.rg_knn_build_dist(self.h, which, k, int(gather), _lib.ptr(idx, C.c_uint32), _lib.ptr(dist, C.c_float)))
         return idx, dist
 
-    def dist_timings(self) -> dict:
+    def dist_timings(self, which: int | None = None) -> dict:
+        """Phase times of the last distributed build (of graph `which` when given)."""
         t = DistTimings()
-        self._chk(self.lib.rg_get_dist_timings(self.h, C.byref(t)))
+        if which is None:
+            self._chk(self.lib.rg_get_dist_timings(self.h, C.byref(t)))
+        else:
+            self._chk(self.lib.rg_get_dist_timings_of(self.h, which, C.byref(t)))
         return t.as_dict()
 
     def knn_kprime(self, which: int, k: int) -> int:

@@ -142,3 +142,46 @@ def sketches(n: int, seed: int = SEED_KNN + 7, mean_size: int = 60, share_frac: 
     offsets[1:] = np.cumsum([len(h) for h in lists])
     hashes = np.concatenate(lists) if n else np.zeros(0, np.uint64)
     return hashes.astype(np.uint64), offsets
+
+
+def knn_tables_parallel(n: int, s: int, seed: int = SEED_KNN, threads: int = 8, flight: bool = False):
+    """The generator of knn_tables with one random stream per block of 65536 rows (seeded by [seed, block]) so that the
+    blocks can be drawn by several threads: same distributions, a different (still deterministic, thread-count
+    independent) table.  Used for the 5M-row shape, where the single-stream generator costs minutes."""
+    master = np.random.default_rng(seed)
+    g = max(50, n // 2000)
+    comp = master.dirichlet(8.0 * np.ones(NBINS), g)
+    abund = master.lognormal(1.5, 1.2, (g, s))
+    abund[master.random((g, s)) < 0.3] = 0.0
+    tnf = np.empty((n, NBINS), np.float64)
+    cov = np.empty((n, 2 * s), np.float64)
+    genome = np.empty(n, np.int64)
+    step = 65536
+
+    def block(bi):
+        b, e = bi * step, min(n, (bi + 1) * step)
+        rng = np.random.default_rng([seed, bi])
+        gen = rng.integers(0, g, e - b)
+        genome[b:e] = gen
+        length = np.rint(np.exp(rng.uniform(np.log(2000.0), np.log(500000.0), e - b))).astype(np.int64)
+        counts = rng.multinomial(length - 3, comp[gen]).astype(np.float64)
+        if flight:
+            x = np.log(counts + 1.0)
+            tnf[b:e] = x - x.mean(axis=1, keepdims=True)
+        else:
+            counts[counts == 0] = 1.0
+            freq = counts / counts.sum(axis=1, keepdims=True)
+            tnf[b:e] = np.log(freq / freq.mean(axis=1, keepdims=True))
+        mean = abund[gen] * rng.lognormal(0.0, 0.1, (e - b, s))
+        var = mean * (1.0 + 3.0 * rng.random((e - b, s)))
+        cov[b:e, 0::2] = mean
+        cov[b:e, 1::2] = var
+
+    nb = (n + step - 1) // step
+    if threads > 1:
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(block, range(nb)))
+    else:
+        for bi in range(nb):
+            block(bi)
+    return tnf, cov, genome
