@@ -35,8 +35,17 @@ def rows(rep):
         yield d
 
 
+def source_hashes():
+    """sha1 of every kernel source: bench.py refuses a roofline.traffic figure whose kernel file changed since the capture"""
+    import glob
+    import hashlib
+    import os
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rosella_b200", "csrc")
+    return {os.path.basename(f): hashlib.sha1(open(f, "rb").read()).hexdigest() for f in sorted(glob.glob(os.path.join(root, "*.cu*")))}
+
+
 if __name__ == "__main__":
-    res = {"reports": sys.argv[2:], "kernels": []}
+    res = {"reports": sys.argv[2:], "source_sha1": source_hashes(), "kernels": []}
     for rep in sys.argv[2:]:
         res["kernels"] += list(rows(rep))
     json.dump(res, open(sys.argv[1], "w"), indent=1)

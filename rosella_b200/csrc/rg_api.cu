@@ -99,6 +99,9 @@ void rg_destroy(rg_handle *h) {
         if (ev) cudaEventDestroy(ev);
     for (auto &st : h->sym_stream)
         if (st) cudaStreamDestroy(st);
+    for (auto &st : h->tnf_stream)
+        if (st) cudaStreamDestroy(st);
+    if (h->tnf_ev) cudaEventDestroy(h->tnf_ev);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }

@@ -98,6 +98,8 @@ struct rg_handle {
     DevBuf tnf_tables;        // 256 B little-endian window -> bin LUT, then 256 B byte-class table
     DevBuf chunk_start;       // u64 [n+1] exclusive scan of chunks per record
     uint64_t tnf_chunks = 0;
+    cudaStream_t tnf_stream[2] = {};   // the two lanes of the pipelined rg_tnf_count_ascii
+    cudaEvent_t tnf_ev = nullptr;
 };
 
 int32_t rg_fail(rg_handle *h, int32_t code, const char *fmt, ...);

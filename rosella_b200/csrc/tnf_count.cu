@@ -31,6 +31,16 @@ __global__ void tnf_freq_kernel(const uint32_t *__restrict__ counts, uint64_t n,
 
 }  // namespace
 
+// records [0, n) of a counts slab, on `stream` (the pipelined ASCII path)
+int32_t rg_tnf_launch_freq_range(rg_handle *h, cudaStream_t stream, const uint32_t *counts, uint64_t n, uint64_t *nkmers, double *freqs) {
+    if (n == 0) return RG_OK;
+    const int wpb = 8;
+    tnf_freq_kernel<<<(unsigned)((n + wpb - 1) / wpb), wpb * 32, 0, stream>>>(counts, n, nkmers, freqs);
+    RG_CUDA(h, cudaGetLastError());
+    h->tm.kernel_launches += 1;
+    return RG_OK;
+}
+
 int32_t rg_tnf_launch_freq(rg_handle *h) {
     if (h->tnf_n == 0) return RG_OK;
     const int wpb = 8;

@@ -296,6 +296,21 @@ int32_t rg_tnf_launch_packed2(rg_handle *h) {
     return RG_OK;
 }
 
+// records [0, n) described by offsets / chunk_start (device), counted into `counts`, on `stream`
+int32_t rg_tnf_launch_ascii2_range(rg_handle *h, cudaStream_t stream, const uint64_t *offsets, const uint64_t *chunk_start,
+                                   uint64_t n, uint64_t n_chunks, uint32_t *counts) {
+    if (n_chunks == 0) return RG_OK;
+    uint64_t per;
+    const unsigned grid = plan_grid(h, n_chunks, per);
+    auto kern = tnf_count_ascii2_kernel;
+    RG_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2)));
+    kern<<<grid, T2, sizeof(Smem2), stream>>>((const uint8_t *)h->ascii.p, offsets, chunk_start, n, n_chunks, per,
+                                              (const uint8_t *)h->tnf_tables.p, counts);
+    RG_CUDA(h, cudaGetLastError());
+    h->tm.kernel_launches += 1;
+    return RG_OK;
+}
+
 int32_t rg_tnf_launch_ascii2(rg_handle *h) {
     if (h->tnf_chunks == 0) return RG_OK;
     uint64_t per;

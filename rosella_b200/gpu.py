@@ -107,11 +107,12 @@ class Context:
     def _tnf_out(self, n):
         return np.zeros((n, NBINS), np.uint32), np.zeros(n, np.uint64), np.zeros((n, NBINS), np.float64)
 
-    def tnf_count_ascii(self, seq, offsets):
+    def tnf_count_ascii(self, seq, offsets, out=None):
+        """out: optional (counts u32[n,136], n_kmers u64[n], freqs f64[n,136]) host arrays to fill (e.g. pinned, reused)."""
         seq = np.ascontiguousarray(seq, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint64)
         n = len(offsets) - 1
-        counts, nk, freqs = self._tnf_out(n)
+        counts, nk, freqs = out if out is not None else self._tnf_out(n)
         self._chk(self.lib.rg_tnf_count_ascii(self.h, _lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n,
                                               _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
                                               _lib.ptr(freqs, C.c_double)))
@@ -386,11 +387,12 @@ class Multi:
         e = int(off[-1])
         return off, nbr[:e].copy(), w[:e].copy(), disc[:nd.value].copy()
 
-    def tnf_count_ascii(self, seq, offsets):
+    def tnf_count_ascii(self, seq, offsets, out=None):
         seq = np.ascontiguousarray(seq, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint64)
         n = len(offsets) - 1
-        counts, nk, freqs = np.zeros((n, NBINS), np.uint32), np.zeros(n, np.uint64), np.zeros((n, NBINS), np.float64)
+        counts, nk, freqs = out if out is not None else (np.zeros((n, NBINS), np.uint32), np.zeros(n, np.uint64),
+                                                         np.zeros((n, NBINS), np.float64))
         self._chk(self.lib.rg_multi_tnf_count_ascii(self.m, _lib.ptr(seq, C.c_uint8), _lib.ptr(offsets, C.c_uint64), n,
                                                     _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
                                                     _lib.ptr(freqs, C.c_double)))

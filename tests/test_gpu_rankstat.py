@@ -50,3 +50,16 @@ def test_rank_stat_5000_against_the_restatement(ctx):
     t = ctx.timings()
     print(f"n={n}: distances {t['select_ms']:.1f} ms, ranks + statistic {t['rescore_ms']:.1f} ms")
     assert (np.diff(sk, axis=1) >= 0).all() and (idx != np.arange(n, dtype=np.uint32)[:, None]).all()
+
+
+def test_out_of_memory_is_an_error_return(ctx):
+    """RG_ERR_OOM, not a crash: 200 000 rows need 9 arrays of 2e10 doubles; the handle stays usable afterwards."""
+    from rosella_b200 import gpu
+    n = 200_000
+    tnf = np.zeros((n, 136)); cov = np.ones((n, 2)); lengths = np.full(n, 5000.0)
+    with pytest.raises(gpu.RosellaGpuError) as e:
+        ctx.rank_stat(tnf, cov, lengths, k=5, condensed=False)
+    assert e.value.code == -4 and "cudaMalloc" in str(e.value)
+    t, c, _ = synth.knn_tables(300, 2, seed=3, flight=True)
+    stat, _, _ = ctx.rank_stat(t, c, np.full(300, 1000.0))
+    assert np.isfinite(stat).all()
