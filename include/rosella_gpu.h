@@ -232,6 +232,11 @@ rg_handle *rg_multi_handle(rg_multi *m, int32_t i);     /* options, timings; do 
 int32_t rg_multi_knn_build(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
                            uint32_t k, uint32_t variant, uint32_t which_mask, uint32_t *tnf_idx, float *tnf_dist,
                            uint32_t *depth_idx, float *depth_dist);
+/* the same with the rows' MinHash sketches (rg_knn_load_sketches): the depth graph is DepthDistance in full */
+int32_t rg_multi_knn_build_sketched(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
+                                    uint32_t k, uint32_t variant, uint32_t which_mask, const uint64_t *hashes,
+                                    const uint64_t *offsets, double scale, uint32_t *tnf_idx, float *tnf_dist,
+                                    uint32_t *depth_idx, float *depth_dist);
 int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d,
                                   uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges, uint64_t *offsets,
                                   uint32_t *neighbours, float *weights, uint64_t *n_disconnected, uint32_t *disconnected);
@@ -251,6 +256,19 @@ int32_t rg_multi_tnf_count_ascii(rg_multi *m, const uint8_t *seq, const uint64_t
  * 9 x 8 x n (n - 1) / 2 bytes of HBM (RG_ERR_OOM beyond).  Timings: select_ms = distances, rescore_ms = ranks. */
 int32_t rg_rank_stat(rg_handle *h, const double *tnf, const double *cov, const double *lengths, uint64_t n, uint32_t d,
                      uint32_t s, uint32_t k, double *stat_condensed, uint32_t *idx, double *stat_knn);
+
+/* ------------------------------------------------------------------ cluster search helpers */
+/* condensed_pairwise_distance (src/clustering/cluster_utils.rs:7-34): Euclidean distance of all row pairs i < j of the
+ * n x d f64 matrix, condensed order, NaN -> 0. */
+int32_t rg_condensed_euclidean(rg_handle *h, const double *data, uint64_t n, uint32_t d, double *out /* n(n-1)/2 */);
+/* silhouette_score (cluster_utils.rs:38-120) computed from the points, not from the O(n^2) distance vector:
+ * labels[i] in [0, n_clusters) or -1 for a point in no cluster (an outlier: it gets no score and belongs to no cluster,
+ * as in the reference's cluster map).  *score = sum of the per-point values / n (:119); per_point (may be NULL) gets s of
+ * every clustered point, 0 elsewhere.  One stated deviation: `a` is the mean distance to ALL other members of the point's
+ * cluster — the reference averages over `indices.iter().skip(*i)` of a HashSet (:57), which depends on the hash seed of
+ * the process and is not reproducible.  select_ms of rg_timings = the kernel. */
+int32_t rg_silhouette(rg_handle *h, const double *data, uint64_t n, uint32_t d, const int32_t *labels, uint32_t n_clusters,
+                      double *score, double *per_point);
 
 /* ------------------------------------------------------------------ graph post-ops */
 /* keep[i*k+j] = 1 when edge j of node i survives mutual_knn / intersect

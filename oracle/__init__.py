@@ -38,7 +38,7 @@ def lib() -> C.CDLL:
             build()
         _lib = C.CDLL(_LIB_PATH)
         _lib.orc_normalize.restype = C.c_size_t
-        for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat", "orc_min_jaccard"):
+        for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat", "orc_min_jaccard", "orc_silhouette"):
             getattr(_lib, f).restype = C.c_double
         for f in ("orc_tnf_distance_f32", "orc_depth_distance_f32", "orc_sketch_distance_f32", "orc_depth_distance_sketch_f32"):
             getattr(_lib, f).restype = C.c_float
@@ -200,6 +200,26 @@ def knn_depth_sketch(cov, hashes, offsets, k: int, variant: int = RUST, scale: f
                                _p(offsets, C.c_uint64), C.c_double(scale), qp, C.c_uint64(nq), C.c_uint32(k),
                                _p(idx, C.c_uint32), _p(dist, C.c_float), C.c_int(threads))
     return idx, dist
+
+
+def condensed_euclidean(data) -> np.ndarray:
+    """condensed_pairwise_distance, src/clustering/cluster_utils.rs:7-34."""
+    data = np.ascontiguousarray(data, np.float64)
+    n, d = data.shape
+    out = np.zeros(n * (n - 1) // 2)
+    lib().orc_condensed_euclidean(_p(data, C.c_double), C.c_uint64(n), C.c_uint32(d), _p(out, C.c_double))
+    return out
+
+
+def silhouette(dist, labels, n_clusters: int):
+    """silhouette_score of cluster_utils.rs:38-120 on a condensed distance vector (a = mean over all other members).
+    -> (score, per-point values)"""
+    dist = np.ascontiguousarray(dist, np.float64)
+    labels = np.ascontiguousarray(labels, np.int32)
+    n = len(labels)
+    pp = np.zeros(n)
+    score = lib().orc_silhouette(_p(dist, C.c_double), C.c_uint64(n), _p(labels, C.c_int32), C.c_uint32(n_clusters), _p(pp, C.c_double))
+    return score, pp
 
 
 def max_threads() -> int:

@@ -93,6 +93,10 @@ void orc_knn_depth_sketch(const double *cov, uint64_t n, uint32_t width, int var
 
 void orc_coverage_distance_condensed(const double *cov, uint64_t n, uint32_t s, double *out, int threads);
 
+/* cluster_utils.rs:7-34 and :38-120 (silhouette with `a` over all other members, see oracle_sketch.c) */
+void orc_condensed_euclidean(const double *data, uint64_t n, uint32_t d, double *out);
+double orc_silhouette(const double *dist, uint64_t n, const int32_t *labels, uint32_t n_clusters, double *per_point);
+
 int orc_max_threads(void);
 
 #ifdef __cplusplus

@@ -117,3 +117,49 @@ void orc_coverage_distance_condensed(const double *cov, uint64_t n, uint32_t s, 
     }
     (void)threads;
 }
+
+/* src/clustering/cluster_utils.rs:7-34 condensed_pairwise_distance: Euclidean, NaN -> 0 */
+void orc_condensed_euclidean(const double *data, uint64_t n, uint32_t d, double *out) {
+    uint64_t p = 0;
+    for (uint64_t i = 0; i + 1 < n; ++i)
+        for (uint64_t j = i + 1; j < n; ++j, ++p) {
+            double r = 0.0;
+            for (uint32_t c = 0; c < d; ++c) { const double t = data[i * d + c] - data[j * d + c]; r += t * t; }
+            r = sqrt(r);
+            out[p] = isnan(r) ? 0.0 : r;
+        }
+}
+
+/* cluster_utils.rs:38-120 silhouette_score from a condensed distance vector, with `a` = mean over ALL other members of
+ * the point's cluster (the reference's `indices.iter().skip(*i)` over a HashSet, :57, depends on the hash seed).
+ * labels[i] in [0, n_clusters) or -1.  Sums run over members in increasing point id.  per_point may be NULL. */
+double orc_silhouette(const double *dist, uint64_t n, const int32_t *labels, uint32_t n_clusters, double *per_point) {
+    if (n_clusters <= 1) return 0.0;                                    /* :39-41 */
+    double total = 0.0;
+    double *sums = (double *)malloc(sizeof(double) * n_clusters);
+    uint64_t *cnts = (uint64_t *)malloc(sizeof(uint64_t) * n_clusters);
+    for (uint32_t c = 0; c < n_clusters; ++c)
+        for (uint64_t i = 0; i < n; ++i) {                              /* clusters, then members: the order of :106-111 */
+            if (labels[i] != (int32_t)c) continue;
+            for (uint32_t k = 0; k < n_clusters; ++k) { sums[k] = 0.0; cnts[k] = 0; }
+            for (uint64_t j = 0; j < n; ++j) {
+                if (j == i || labels[j] < 0) continue;
+                const uint64_t lo = i < j ? i : j, hi = i < j ? j : i;
+                const uint64_t index = n * (n - 1) / 2 - (n - lo) * (n - lo - 1) / 2 + hi - lo - 1;   /* :126-132 */
+                sums[labels[j]] += dist[index];
+                cnts[labels[j]] += 1;
+            }
+            double a = sums[c] / (double)(cnts[c] ? cnts[c] : 1);       /* :66-69 */
+            double b = -1.0;                                            /* :53 */
+            for (uint32_t k = 0; k < n_clusters; ++k) {
+                if (k == c) continue;
+                const double m = sums[k] / (double)(cnts[k] ? cnts[k] : 1);   /* :84-88 */
+                if (m < b || b < 0.0) b = m;                            /* :90-92 */
+            }
+            const double s = (b - a) / (a > b ? a : b);                 /* :94 */
+            if (per_point) per_point[i] = s;
+            total += s;
+        }
+    free(sums); free(cnts);
+    return total / (double)n;                                           /* :119 */
+}

@@ -135,6 +135,26 @@ int32_t rg_multi_knn_build(rg_multi *m, const double *tnf, const double *cov, ui
     });
 }
 
+// rg_multi_knn_build with the MinHash sketches of the rows: the depth graph is DepthDistance in full (embedder.rs:133-171).
+// Every device joins the sketches on its own copy (rg_knn_load_sketches is local work).
+int32_t rg_multi_knn_build_sketched(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
+                                    uint32_t k, uint32_t variant, uint32_t which_mask, const uint64_t *hashes,
+                                    const uint64_t *offsets, double scale, uint32_t *tnf_idx, float *tnf_dist,
+                                    uint32_t *depth_idx, float *depth_dist) {
+    if (!m) return RG_ERR_INVALID;
+    const bool want_tnf = which_mask & (1u << RG_GRAPH_TNF), want_depth = which_mask & (1u << RG_GRAPH_DEPTH);
+    auto bad = [&](const char *msg) { m->err = msg; return (int32_t)RG_ERR_INVALID; };
+    if (!want_depth || !cov || !depth_idx || !depth_dist || !offsets) return bad("rg_multi_knn_build_sketched: the depth graph, its table and the sketch offsets are required");
+    if (want_tnf && (!tnf || !tnf_idx || !tnf_dist)) return bad("rg_multi_knn_build_sketched: TNF graph requested with a NULL pointer");
+    return run_all(m, [&](int, rg_handle *h) -> int32_t {
+        RG_TRY(rg_knn_load_dist(h, want_tnf ? tnf : nullptr, cov, n, d, s, variant, 0));
+        RG_TRY(rg_comm_agree(h, rg_knn_load_sketches(h, hashes, offsets, n, scale)));
+        RG_TRY(rg_knn_build_dist(h, RG_GRAPH_DEPTH, k, 0, depth_idx, depth_dist));
+        if (want_tnf) RG_TRY(rg_knn_build_dist(h, RG_GRAPH_TNF, k, 0, tnf_idx, tnf_dist));
+        return RG_OK;
+    });
+}
+
 int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *cov, uint64_t n, uint32_t d,
                                   uint32_t s, uint32_t k, uint32_t variant, uint32_t keep_n_edges, uint64_t *offsets,
                                   uint32_t *neighbours, float *weights, uint64_t *n_disconnected, uint32_t *disconnected) {

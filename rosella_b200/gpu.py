@@ -363,6 +363,20 @@ class Multi:
     def handle(self, i: int) -> Context:
         return Context(self.devices[i], _borrowed=self.lib.rg_multi_handle(self.m, i))
 
+    def knn_build_sketched(self, tnf, cov, hashes, offsets, k: int, scale: float = 0.1, variant: int = VARIANT_RUST,
+                           which_mask: int = 3):
+        tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
+        hashes, offsets = np.ascontiguousarray(hashes, np.uint64), np.ascontiguousarray(offsets, np.uint64)
+        n, s = cov.shape[0], cov.shape[1] // 2
+        d = tnf.shape[1] if tnf is not None else NBINS
+        ti, td = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        di, dd = np.zeros((n, k), np.uint32), np.zeros((n, k), np.float32)
+        self._chk(self.lib.rg_multi_knn_build_sketched(self.m, _lib.ptr(tnf, C.c_double), _lib.ptr(cov, C.c_double), n, d, s, k,
+                                                       variant, which_mask, _lib.ptr(hashes, C.c_uint64),
+                                                       _lib.ptr(offsets, C.c_uint64), scale, _lib.ptr(ti, C.c_uint32),
+                                                       _lib.ptr(td, C.c_float), _lib.ptr(di, C.c_uint32), _lib.ptr(dd, C.c_float)))
+        return (ti, td), (di, dd)
+
     def knn_build(self, tnf, cov, k: int, variant: int = VARIANT_RUST, which_mask: int = 3):
         tnf, cov = _lib.as_f64(tnf), _lib.as_f64(cov)
         n = (tnf if tnf is not None else cov).shape[0]

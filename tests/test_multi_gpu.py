@@ -95,6 +95,12 @@ def test_multi_two_devices_equal_one(ctx, n, s, k):
         assert np.array_equal(mti, ti) and np.array_equal(mtd, td)
         t0, t1 = m.handle(0).dist_timings(), m.handle(1).dist_timings()
         assert t0["load_bcast_ms"] > 0 and t1["load_h2d_ms"] < t0["load_h2d_ms"] + 1e-3
+        hashes, offs = synth.sketches(n, seed=4, mean_size=30, share_frac=0.2)
+        ctx.knn_load(None, cov)
+        ctx.knn_load_sketches(hashes, offs, 0.1)
+        si, sd, _ = ctx.knn_search(gpu.GRAPH_DEPTH, k)
+        (_, _), (msi, msd) = m.knn_build_sketched(tnf, cov, hashes, offs, k)
+        assert np.array_equal(msi, si) and np.array_equal(msd, sd) and not np.array_equal(msi, di)
         got = m.knn_build_mutual(tnf, cov, k, 6)
         want = ctx.knn_build_mutual(tnf, cov, k, 6)
         for a, b in zip(got, want):
