@@ -21,7 +21,7 @@ SYMBOLS = [
     "rg_knn_load", "rg_knn_load_sketches", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
     "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
-    "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat",
+    "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat", "rg_condensed_euclidean", "rg_silhouette",
     "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
     "rg_knn_build_dist", "rg_get_dist_timings", "rg_get_dist_timings_of",
     "rg_multi_create", "rg_multi_destroy", "rg_multi_last_error", "rg_multi_size", "rg_multi_handle", "rg_multi_knn_build", "rg_multi_knn_build_sketched",
@@ -107,6 +107,8 @@ def load() -> C.CDLL:
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
         "rg_knn_flagged_rows": (C.c_int32, [vp, u32p, f32p, f32p, C.c_uint64, C.POINTER(C.c_uint64)]),
         "rg_rank_stat": (C.c_int32, [vp, f64p, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, f64p, u32p, f64p]),
+        "rg_condensed_euclidean": (C.c_int32, [vp, f64p, C.c_uint64, C.c_uint32, f64p]),
+        "rg_silhouette": (C.c_int32, [vp, f64p, C.c_uint64, C.c_uint32, C.POINTER(C.c_int32), C.c_uint32, f64p, f64p]),
         "rg_knn_refilter": (C.c_int32, [vp, C.c_uint32, u64p, u32p, f32p, u64p, u32p]),
         "rg_knn_build_subset": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, u64p, C.c_uint64, C.c_uint32,
                                             C.c_uint32, C.c_uint32, u32p, f32p, u32p, f32p]),

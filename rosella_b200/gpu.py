@@ -313,6 +313,24 @@ class Context:
                                         n, d, s, k, _lib.ptr(stat, C.c_double), _lib.ptr(idx, C.c_uint32), _lib.ptr(sk, C.c_double)))
         return stat, idx, sk
 
+    def condensed_euclidean(self, data):
+        """condensed_pairwise_distance (cluster_utils.rs:7-34) -> f64 [n(n-1)/2]"""
+        data = _lib.as_f64(data)
+        n, d = data.shape
+        out = np.zeros(n * (n - 1) // 2, np.float64)
+        self._chk(self.lib.rg_condensed_euclidean(self.h, _lib.ptr(data, C.c_double), n, d, _lib.ptr(out, C.c_double)))
+        return out
+
+    def silhouette(self, data, labels, n_clusters: int):
+        """silhouette_score (cluster_utils.rs:38-120) from the points -> (score, per-point values)"""
+        data = _lib.as_f64(data)
+        labels = np.ascontiguousarray(labels, np.int32)
+        n, d = data.shape
+        score, pp = C.c_double(0.0), np.zeros(n, np.float64)
+        self._chk(self.lib.rg_silhouette(self.h, _lib.ptr(data, C.c_double), n, d, _lib.ptr(labels, C.c_int32), n_clusters,
+                                         C.byref(score), _lib.ptr(pp, C.c_double)))
+        return score.value, pp
+
     # ------------------------------------------------------------------ graph post-ops
     def graph_mutual(self, idx, keep_n_edges: int):
         idx = np.ascontiguousarray(idx, np.uint32)

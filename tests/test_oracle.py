@@ -223,3 +223,23 @@ def test_rank_statistic_restatement_is_pinned(golden_dir, s):
     groups = np.unique(g[f"cov_dist_s{s}"].round(12), return_counts=True)[1]
     assert np.abs(cr2 - cr).max() <= groups[groups < 300].max() and np.array_equal(kr2, kr)
     assert np.median(np.abs(st2 - st) / st) < 1e-12
+
+
+def test_silhouette_restatement_matches_the_textbook_definition():
+    """oracle.silhouette (cluster_utils.rs:38-120 with `a` over all other members) against scikit-learn on clean clusters,
+    and the reference's corner cases: one cluster -> 0, a cluster of one -> a = 0 -> s = 1, outliers (label -1) unscored,
+    the score divides by ALL rows (:119)."""
+    from scipy.spatial.distance import pdist
+    from sklearn.metrics import silhouette_samples
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.normal(c, 0.3, (40, 2)) for c in ((0, 0), (3, 0), (0, 4))])
+    lab = np.repeat([0, 1, 2], 40).astype(np.int32)
+    d = oracle.condensed_euclidean(x)
+    assert np.array_equal(d, pdist(x))
+    score, pp = oracle.silhouette(d, lab, 3)
+    ss = silhouette_samples(x, lab)
+    assert np.allclose(pp, ss, rtol=1e-12, atol=1e-14) and abs(score - ss.mean()) < 1e-14
+    assert oracle.silhouette(d, np.zeros(120, np.int32), 1)[0] == 0.0
+    lab2 = lab.copy(); lab2[:10] = -1; lab2[10] = 3
+    score2, pp2 = oracle.silhouette(d, lab2, 4)
+    assert (pp2[:10] == 0).all() and pp2[10] == 1.0 and abs(score2 - pp2.sum() / 120) < 1e-15
