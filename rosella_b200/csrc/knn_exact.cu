@@ -16,8 +16,8 @@
 // (1) and (2) always involve two rows whose values share one FP32 rounding in one column, so they can be enumerated:
 // per (sample, field) column the f64 values are sorted, every run of equal FP32 roundings that holds more than one f64
 // value yields its cross pairs, and each pair becomes an EXTRA CANDIDATE of both rows — the f64 re-evaluation then
-// sees the pair whatever the select kernel made of it.  Runs longer than RUNCAP (near-duplicate clusters) mark their
-// rows for the exhaustive f64 pass instead.  Cost: 2 S radix sorts of n (f64, u32) pairs per load.
+// sees the pair whatever the select kernel made of it.  A row with more than 64 such partners in one column (a cluster of
+// near-duplicates) takes the exhaustive f64 pass instead.  Cost: 2 S radix sorts of n (f64, u32) pairs per load.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_reduce.cuh>
 #include <cub/device/device_select.cuh>
@@ -25,8 +25,6 @@
 #include "rg_internal.cuh"
 
 namespace {
-
-constexpr uint32_t RUNCAP = 128;
 
 // field 0: mean + eps (:600-601); field 1: max(var + eps, 1) (:602-609) — the values knn_transform.cu rounds to FP32
 __global__ void column_keys_kernel(const double *__restrict__ cov, uint32_t n, uint32_t s, uint32_t smp, int field,
@@ -39,40 +37,44 @@ __global__ void column_keys_kernel(const double *__restrict__ cov, uint32_t n, u
     rows[i] = i;
 }
 
-// keys sorted ascending.  The first element of every run of equal FP32 roundings checks whether the run holds more
-// than one f64 value (sorted: first != last) and, if so, emits the cross pairs in both directions.
+// keys sorted ascending.  Every element looks at the run of elements that share its FP32 rounding: the members whose
+// f64 value differs from its own are the rows the select kernel may misjudge against this row.  Up to EMIT_CAP of them
+// become extra candidates of this row (one directed pair each; the other row emits its own direction); a row with more
+// partners takes the exhaustive pass instead.  The decision is per row, so one stray value inside a run of 300 000
+// identical ones (variances clamped to exactly 1.0 plus one variance of 1 + 3e-8) costs one extra candidate per member
+// and one exhaustive row — not 300 000 exhaustive rows.
+constexpr uint32_t EMIT_CAP = 64;
+
 __global__ void collide_kernel(const double *__restrict__ keys, const uint32_t *__restrict__ rows, uint32_t n,
                                uint64_t *__restrict__ pairs, unsigned long long *__restrict__ n_pairs, uint64_t cap,
                                uint8_t *__restrict__ row_flag) {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const float k32 = (float)keys[p];
-    if (p > 0 && (float)keys[p - 1] == k32) return;          // not the start of a run
-    if (p + 1 >= n || (float)keys[p + 1] != k32) return;     // run of one
-    uint32_t lo = p + 1, hi = n;                              // end of the run: the FP32 rounding is monotonic
-    while (lo < hi) {
-        const uint32_t mid = lo + (hi - lo) / 2;
-        if ((float)keys[mid] == k32) lo = mid + 1; else hi = mid;
-    }
+    const double v = keys[p];
+    const float k32 = (float)v;
+    const bool left = p > 0 && (float)keys[p - 1] == k32, right = p + 1 < n && (float)keys[p + 1] == k32;
+    if (!left && !right) return;                              // alone in its FP32 rounding
+    uint32_t lo = 0, hi = p;                                  // run of the FP32 rounding: [begin, end) (the rounding is monotonic)
+    while (lo < hi) { const uint32_t mid = lo + (hi - lo) / 2; if ((float)keys[mid] < k32) lo = mid + 1; else hi = mid; }
+    const uint32_t begin = lo;
+    lo = p + 1; hi = n;
+    while (lo < hi) { const uint32_t mid = lo + (hi - lo) / 2; if ((float)keys[mid] <= k32) lo = mid + 1; else hi = mid; }
     const uint32_t end = lo;
-    if (keys[end - 1] == keys[p]) return;                     // one f64 value: FP32 equality is f64 equality
-    if (end - p > RUNCAP) {
-        for (uint32_t i = p; i < end; ++i) row_flag[rows[i]] = 1;
-        return;
-    }
-    for (uint32_t i = p; i < end; ++i)
-        for (uint32_t j = i + 1; j < end; ++j) {
-            if (keys[i] == keys[j]) continue;
-            const uint64_t ri = rows[i], rj = rows[j];
-            const unsigned long long slot = atomicAdd(n_pairs, 2ull);
-            if (slot + 2 <= cap) {
-                pairs[slot] = (ri << 32) | rj;
-                pairs[slot + 1] = (rj << 32) | ri;
-            } else {
-                row_flag[ri] = 1;
-                row_flag[rj] = 1;
-            }
-        }
+    if (keys[begin] == keys[end - 1]) return;                 // one f64 value: FP32 equality is f64 equality
+    lo = begin; hi = p;                                       // this row's f64 value inside the run: [gb, ge)
+    while (lo < hi) { const uint32_t mid = lo + (hi - lo) / 2; if (keys[mid] < v) lo = mid + 1; else hi = mid; }
+    const uint32_t gb = lo;
+    lo = p + 1; hi = end;
+    while (lo < hi) { const uint32_t mid = lo + (hi - lo) / 2; if (keys[mid] <= v) lo = mid + 1; else hi = mid; }
+    const uint32_t ge = lo;
+    const uint32_t others = (gb - begin) + (end - ge);
+    const uint64_t me = rows[p];
+    if (others > EMIT_CAP) { row_flag[me] = 1; return; }
+    const unsigned long long slot = atomicAdd(n_pairs, (unsigned long long)others);
+    if (slot + others > cap) { row_flag[me] = 1; return; }    // the host grows the buffer and scans again
+    uint64_t w = slot;
+    for (uint32_t o = begin; o < gb; ++o) pairs[w++] = (me << 32) | rows[o];
+    for (uint32_t o = ge; o < end; ++o) pairs[w++] = (me << 32) | rows[o];
 }
 
 }  // namespace
@@ -121,12 +123,11 @@ int32_t rg_build_collision_patches(rg_handle *h, uint64_t n64, uint32_t s, uint3
         RG_CUDA(h, cudaMemcpyAsync(&found, ctr.p, sizeof(found), cudaMemcpyDeviceToHost, h->stream));
         RG_CUDA(h, cudaStreamSynchronize(h->stream));
         if (found <= cap) break;
-        // more pairs than the buffer holds (dense data): grow once to what was counted and scan again; should even that
-        // fail, the pairs that did not fit have marked their rows for the exhaustive pass (collide_kernel)
-        if (attempt == 0 && rg_reserve(h, pairs, (found + found / 4) * sizeof(uint64_t)) != RG_OK) break;
+        // more pairs than the buffer holds (dense data): grow to what was counted and scan again (same count, so it fits)
+        if (attempt == 1) return rg_fail(h, RG_ERR_STATE, "collision scan: pair count changed between two scans");
+        RG_TRY(rg_reserve(h, pairs, (found + found / 4) * sizeof(uint64_t)));
     }
-    const uint64_t cap = pairs.cap / sizeof(uint64_t);
-    const uint64_t count = found < cap ? found : cap / 2 * 2;
+    const uint64_t count = found;
     // the collision pairs stay on the handle (unsorted, duplicates allowed): rg_rebuild_extras sorts and merges them
     // with the pairs of rows that share sketch hashes (rg_knn_load_sketches)
     RG_TRY(rg_reserve(h, h->coll_pairs, (count ? count : 1) * sizeof(uint64_t)));

@@ -333,8 +333,13 @@ exact_rows_kernel(const ExactArgs a) {
                 float acc0 = 0.f, cnt0 = 0.f, acc1 = 0.f, cnt1 = 0.f;
                 depthk::SignTrack unused;
                 const float4 *ref = a.cov_t + (uint64_t)g * S * RG_TILE + lane;
+                // two samples ahead in registers: the loop is a chain of ~150-cycle evaluations fed by global loads, and a
+                // CTA has only 8 warps to hide them behind
+                float4 b0 = ref[0], b1 = S > 1 ? ref[RG_TILE] : b0;
                 for (uint32_t smp = 0; smp < S; ++smp) {
-                    const float4 b = ref[(size_t)smp * RG_TILE];
+                    const float4 b = b0;
+                    b0 = b1;
+                    if (smp + 2 < S) b1 = ref[(size_t)(smp + 2) * RG_TILE];
                     const ulonglong2 xy = q4[2 * smp], zw = q4[2 * smp + 1];
                     depthk::depth_sample2<VARIANT, false>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc0, cnt0, acc1, cnt1, unused);
                 }
