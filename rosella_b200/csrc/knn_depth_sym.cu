@@ -216,6 +216,16 @@ int32_t build(rg_handle *h, float *cd, uint32_t *ci, uint32_t part, uint32_t n_p
     // Launch m evaluates into buffer m & 1 on evaluation stream m & 1, so the CTAs of launch m + 1 fill the SMs as
     // those of launch m retire; the reducers of launch m follow on their own stream (in launch order: the lists need
     // their candidates by increasing index) and release the buffer for launch m + 2.
+    // an error inside the loop must not return with the three side streams still forked from h->stream (they may be
+    // writing the lists and the distance buffers a later call frees): record it, leave the loop, join, then return it
+    int32_t status = RG_OK;
+#define SYM_CUDA(call)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t e__ = (call);                                                                              \
+        if (e__ != cudaSuccess && status == RG_OK)                                                             \
+            status = rg_fail(h, e__ == cudaErrorMemoryAllocation ? RG_ERR_OOM : RG_ERR_CUDA, "%s failed: %s (%s:%d)", #call, \
+                             cudaGetErrorString(e__), __FILE__, __LINE__);                                     \
+    } while (0)
     uint32_t m = 0;
     for (uint32_t i0 = 0, blk = 0; i0 < n; i0 += B, ++blk) {
         const uint32_t round = blk / n_parts, pos = blk % n_parts;
@@ -226,11 +236,11 @@ int32_t build(rg_handle *h, float *cd, uint32_t *ci, uint32_t part, uint32_t n_p
             const uint32_t jb = std::max(c0, i1);          // first column right of the block
             float *Dm = (float *)h->sym_d.p + (m & 1) * buf_floats, *Dt = (float *)h->sym_t.p + (m & 1) * buf_floats;
             cudaStream_t ev_st = h->sym_stream[m & 1];
-            if (m >= 2) RG_CUDA(h, cudaStreamWaitEvent(ev_st, reduced[m & 1], 0));
+            if (m >= 2) SYM_CUDA(cudaStreamWaitEvent(ev_st, reduced[m & 1], 0));
             kern<<<ni_pad / QB, WARPS * 32, smem, ev_st>>>((const float4 *)h->cov_t.p, n, S, sc, i0, c0 / RG_TILE,
                                                            nc_pad / RG_TILE, Dm, nc_pad, jb < c1 ? Dt : nullptr, ni_pad);
-            RG_CUDA(h, cudaEventRecord(evaluated[m & 1], ev_st));
-            RG_CUDA(h, cudaStreamWaitEvent(red, evaluated[m & 1], 0));
+            SYM_CUDA(cudaEventRecord(evaluated[m & 1], ev_st));
+            SYM_CUDA(cudaStreamWaitEvent(red, evaluated[m & 1], 0));
             topk_reduce_kernel<K><<<(ni + RWARPS - 1) / RWARPS, RWARPS * 32, 0, red>>>(Dm, nc_pad, nc_pad, i0, ni, c0, n, cd, ci);
             h->tm.kernel_launches += 2;
             if (jb < c1) {
@@ -238,11 +248,17 @@ int32_t build(rg_handle *h, float *cd, uint32_t *ci, uint32_t part, uint32_t n_p
                     Dt + (size_t)(jb - c0) * ni_pad, ni_pad, ni_pad, jb, c1 - jb, i0, n, cd, ci);
                 h->tm.kernel_launches += 1;
             }
-            RG_CUDA(h, cudaEventRecord(reduced[m & 1], red));
+            SYM_CUDA(cudaEventRecord(reduced[m & 1], red));
         }
-        RG_CUDA(h, cudaGetLastError());
+        SYM_CUDA(cudaGetLastError());
+        if (status != RG_OK) break;
     }
     // join: everything the lists depend on ends on the reducer stream
+    if (status != RG_OK) {
+        for (auto &st : h->sym_stream) cudaStreamSynchronize(st);
+        return status;
+    }
+#undef SYM_CUDA
     RG_CUDA(h, cudaEventRecord(fork, red));
     RG_CUDA(h, cudaStreamWaitEvent(h->stream, fork, 0));
     return RG_OK;
