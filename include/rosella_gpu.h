@@ -113,7 +113,9 @@ int32_t rg_tnf_fetch(rg_handle *h, uint32_t *counts, uint64_t *n_kmers, double *
  *   cov  n x 2s f64 row-major, interleaved mean,var per sample as MetabatDistance reads them
  *        (coverage_calculator.rs:593-596).
  * Either may be NULL if that graph is never searched.  Non-finite coverage -> RG_ERR_INVALID
- * (the reference panics in Normal::new, coverage_calculator.rs:639). */
+ * (the reference panics in Normal::new, coverage_calculator.rs:639); so is a negative mean (no read depth is negative,
+ * and the FP32 select phase relies on mean + eps >= eps for :619).  The load also scans every coverage column for
+ * f64-distinct values that collide in FP32 and keeps those row pairs as extra candidates of the f64 pass (knn_exact.cu). */
 int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d,
                     uint32_t s, uint32_t variant);
 
@@ -129,7 +131,9 @@ int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, const uint64_
 /* Exact top-k of query rows [q_begin, q_end) against all n loaded rows, self excluded, ascending
  * by (f32 distance, index).  idx/dist: (q_end-q_begin) x k; rows with fewer than k candidates are
  * padded with UINT32_MAX / +inf; n_valid (may be NULL) gets the count per row.
- * Distances are the reference metric evaluated in f64 and truncated to f32 (embedder.rs:125,:170). */
+ * Distances are the reference metric evaluated in f64 and truncated to f32 (embedder.rs:125,:170).
+ * The FP32 select phase is certified per row against its own f64 values; rows that fail are re-evaluated against all
+ * n rows inside the same call (rg_timings.rows_flagged / rows_exact, rg_knn_flagged_rows). */
 int32_t rg_knn_search(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_begin, uint64_t q_end,
                       uint32_t *idx, float *dist, uint32_t *n_valid);
 /* same, outputs are DEVICE pointers; asynchronous on rg_stream(h) */
@@ -144,7 +148,8 @@ int32_t rg_knn_search_dev(rg_handle *h, uint32_t which, uint32_t k, uint64_t q_b
  *      and writes, for EVERY row, a K'-entry candidate list sorted by (distance, index) and padded with
  *      (+inf, UINT32_MAX): cand_dist_dev / cand_idx_dev are device arrays [n][K'], K' = rg_knn_kprime(h, RG_GRAPH_DEPTH, k);
  *   2. the host exchanges the lists so that the owner of rows [q_begin, q_end) holds all parts' lists of those
- *      rows, [n_parts][q_end - q_begin][K'] (an all-to-all; rosella_b200/dist.py does it with NCCL);
+ *      rows, [n_parts][q_end - q_begin][K'] (an all-to-all; rg_knn_build_dist below does all three steps inside the
+ *      library with NCCL — these two calls remain for hosts that bring their own transport);
  *   3. rg_knn_depth_merge_dev merges them and finishes as rg_knn_search_dev does (f64 distances, same outputs).
  * Both calls are asynchronous on rg_stream(h).  Replaces nothing in the reference by itself: it is how
  * EmbedderEngine::build_mutual_kgraph (embedder.rs:31-86) scales past one GPU. */

@@ -118,6 +118,21 @@ def test_multi_two_devices_equal_one(ctx, n, s, k):
 
 @pytest.mark.gpu
 @pytest.mark.skipif("n_gpus() < 2")
+@pytest.mark.parametrize("n", [20, 50, 700])
+def test_multi_two_devices_tiny_tables(ctx, n):
+    """Fewer rows than one 32-row tile per rank (rank 1 owns nothing at n = 20), fewer rows than k."""
+    tnf, cov, _ = synth.knn_tables(n, 3, seed=n)
+    (ti, td), (di, dd) = ctx.knn_build(tnf, cov, 30)
+    with gpu.Multi([0, 1]) as m:
+        (mti, mtd), (mdi, mdd) = m.knn_build(tnf, cov, 30)
+        assert np.array_equal(mti, ti) and np.array_equal(mtd, td) and np.array_equal(mdi, di) and np.array_equal(mdd, dd)
+        got = m.knn_build_mutual(tnf, cov, 30, 3)
+        for a, b in zip(got, ctx.knn_build_mutual(tnf, cov, 30, 3)):
+            assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif("n_gpus() < 2")
 def test_comm_two_ranks_in_two_threads(ctx):
     """The one-process-per-GPU flavour (rg_comm_init + rg_knn_load_dist + rg_knn_build_dist), driven here by two
     threads with one handle each: rank 1 never sees the host tables."""
