@@ -44,7 +44,8 @@ def load() -> C.CDLL:
         "rh_fastx_id": (C.c_char_p, [vp, sz]), "rh_fastx_seq": (C.POINTER(C.c_uint8), [vp]),
         "rh_fastx_offsets": (C.POINTER(C.c_uint64), [vp]),
         "rh_count_kmers": (vp, [C.c_int, C.c_char_p, C.c_char_p, C.c_int]),
-        "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32]),
+        "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32,
+                                        C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_double]),
         "rh_graph_free": (None, [vp]), "rh_graph_nb_nodes": (sz, [vp]), "rh_graph_max_nbng": (sz, [vp]),
         "rh_graph_n_disconnected": (sz, [vp]), "rh_graph_disconnected": (C.POINTER(sz), [vp]),
         "rh_graph_degree": (sz, [vp, C.c_int, sz]),
@@ -206,11 +207,17 @@ class KGraphResult:
 
 
 def build_mutual_kgraph(tnf: np.ndarray, cov: np.ndarray, keep_n_edges: int, n_neighbours: int, max_layers: int = 16,
-                        ef_construction: int = 200, apply_filters: bool = False, variant: int = 0, device: int = 0):
-    """EmbedderEngine::new(contig_data).build_mutual_kgraph(...) (embedder.rs:31-86)"""
+                        ef_construction: int = 200, apply_filters: bool = False, variant: int = 0, device: int = 0,
+                        sketches=None, sketch_scale: float = 0.1):
+    """EmbedderEngine::new(contig_data).build_mutual_kgraph(...) (embedder.rs:31-86); sketches = (hashes u64, offsets u64
+    [n + 1]): the ContigInformation.sketch members (embedder.rs:96)"""
     t = np.ascontiguousarray(tnf, np.float64)
     c = np.ascontiguousarray(cov, np.float64)
-    dp = C.POINTER(C.c_double)
+    dp, up = C.POINTER(C.c_double), C.POINTER(C.c_uint64)
+    sh = so = None
+    if sketches is not None:
+        sh_a, so_a = np.ascontiguousarray(sketches[0], np.uint64), np.ascontiguousarray(sketches[1], np.uint64)
+        sh, so = sh_a.ctypes.data_as(up), so_a.ctypes.data_as(up)
     return KGraphResult(load().rh_build_mutual_kgraph(device, t.ctypes.data_as(dp), t.shape[1], c.ctypes.data_as(dp),
                                                       c.shape[1], t.shape[0], keep_n_edges, n_neighbours, max_layers,
-                                                      ef_construction, int(apply_filters), variant))
+                                                      ef_construction, int(apply_filters), variant, sh, so, sketch_scale))

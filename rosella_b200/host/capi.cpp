@@ -106,15 +106,26 @@ KmerFrequencyTable *rh_count_kmers(int device, const char *assembly, const char 
     return t;
 }
 
+// sketch_hashes / sketch_offsets (n + 1 entries) may be NULL: no sketches
 rh_graph *rh_build_mutual_kgraph(int device, const double *tnf, size_t d, const double *cov, size_t c, size_t n,
                                  size_t keep_n_edges, size_t n_neighbours, size_t max_layers, size_t ef_construction,
-                                 int apply_filters, uint32_t variant) {
+                                 int apply_filters, uint32_t variant, const uint64_t *sketch_hashes,
+                                 const uint64_t *sketch_offsets, double sketch_scale) {
     rh_graph *out = nullptr;
     if (guard([&] {
             Gpu gpu(device);
             std::vector<std::vector<ContigInformation>> info(n);
-            for (size_t i = 0; i < n; ++i) info[i].push_back(ContigInformation{cov + i * c, c, tnf + i * d, d});
+            for (size_t i = 0; i < n; ++i) {
+                ContigInformation ci{cov + i * c, c, tnf + i * d, d};
+                if (sketch_offsets) {
+                    static const uint64_t none = 0;                      // an empty sketch still is a sketch
+                    ci.sketch = sketch_hashes ? sketch_hashes + sketch_offsets[i] : &none;
+                    ci.sketch_len = (size_t)(sketch_offsets[i + 1] - sketch_offsets[i]);
+                }
+                info[i].push_back(ci);
+            }
             EmbedderEngine engine(std::move(info));
+            engine.sketch_scale = sketch_scale;
             auto res = engine.build_mutual_kgraph(gpu, keep_n_edges, n_neighbours, n, max_layers, ef_construction,
                                                   apply_filters != 0, variant);
             out = new rh_graph{std::move(res.first), engine.last_tnf_kgraph, std::move(res.second)};

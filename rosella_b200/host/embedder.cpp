@@ -118,9 +118,25 @@ std::pair<KGraph, std::vector<size_t>> EmbedderEngine::build_mutual_kgraph(Gpu &
     const size_t k = n_neighbours;
     std::vector<uint32_t> ti(n * k), di(n * k);
     std::vector<float> td(n * k), dd(n * k);
-    gpu.check(rg_knn_build(gpu.raw(), tnf.data(), cov.data(), n, (uint32_t)d, (uint32_t)(c / 2), (uint32_t)k, variant,
-                           (1u << RG_GRAPH_TNF) | (1u << RG_GRAPH_DEPTH), ti.data(), td.data(), di.data(), dd.data()),
-              "rg_knn_build");                                           // embedder.rs:32-65
+    bool sketched = false;
+    for (size_t i = 0; i < n && !sketched; ++i) sketched = contig_information[i].at(0).sketch != nullptr;
+    if (!sketched) {
+        gpu.check(rg_knn_build(gpu.raw(), tnf.data(), cov.data(), n, (uint32_t)d, (uint32_t)(c / 2), (uint32_t)k, variant,
+                               (1u << RG_GRAPH_TNF) | (1u << RG_GRAPH_DEPTH), ti.data(), td.data(), di.data(), dd.data()),
+                  "rg_knn_build");                                       // embedder.rs:32-65
+    } else {
+        // DepthDistance with its MinHash factor (embedder.rs:147-164): the sketches go in between load and search
+        std::vector<uint64_t> hashes, offs(n + 1, 0);
+        for (size_t i = 0; i < n; ++i) {
+            const ContigInformation &ci = contig_information[i].at(0);
+            if (ci.sketch) hashes.insert(hashes.end(), ci.sketch, ci.sketch + ci.sketch_len);
+            offs[i + 1] = hashes.size();
+        }
+        gpu.check(rg_knn_load(gpu.raw(), tnf.data(), cov.data(), n, (uint32_t)d, (uint32_t)(c / 2), variant), "rg_knn_load");
+        gpu.check(rg_knn_load_sketches(gpu.raw(), hashes.data(), offs.data(), n, sketch_scale), "rg_knn_load_sketches");
+        gpu.check(rg_knn_search(gpu.raw(), RG_GRAPH_DEPTH, (uint32_t)k, 0, n, di.data(), dd.data(), nullptr), "rg_knn_search");
+        gpu.check(rg_knn_search(gpu.raw(), RG_GRAPH_TNF, (uint32_t)k, 0, n, ti.data(), td.data(), nullptr), "rg_knn_search");
+    }
     KGraph depth_kgraph = kgraph_from_lists(di, dd, n, k);
     last_tnf_kgraph = kgraph_from_lists(ti, td, n, k);
     KGraph kgraph = intersect(gpu, std::move(depth_kgraph), last_tnf_kgraph,

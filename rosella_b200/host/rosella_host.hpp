@@ -101,12 +101,15 @@ class KGraph {
     size_t max_nbng_ = 0;
 };
 
-// embedder.rs:89-104 without the MinHash sketch
+// embedder.rs:89-104.  sketch: finch's Sketch.hashes of the contig (KmerCount.hash, sorted and unique as to_vec()
+// returns them), nullptr = no sketch: DepthDistance then has the factor 1 for every pair.
 struct ContigInformation {
     const double *coverage;
     size_t coverage_len;      // 2 x samples, interleaved mean,var
     const double *tnf;
     size_t tnf_len;
+    const uint64_t *sketch = nullptr;
+    size_t sketch_len = 0;
 };
 
 class EmbedderEngine {        // embedder.rs:15-87
@@ -121,6 +124,7 @@ class EmbedderEngine {        // embedder.rs:15-87
                                                                size_t ef_construction, bool apply_filters = false,
                                                                uint32_t variant = RG_VARIANT_RUST) const;
     std::vector<std::vector<ContigInformation>> contig_information;
+    double sketch_scale = 0.1;          // SketchParams::Scaled.scale of the sketches (contig_sketcher.rs:66-71; cli default 0.1)
     // the TNF graph of the last build (the reference builds it as tnf_kgraph, :65)
     mutable KGraph last_tnf_kgraph;
 };

@@ -219,3 +219,23 @@ def test_build_mutual_kgraph_matches_the_exhaustive_oracle():
     for i in range(n):
         assert f.neighbours(i)[0].tolist() == step2[i]
     assert f.disconnected_nodes == [i for i in range(n) if not step2[i]]
+
+
+@pytest.mark.gpu
+def test_build_mutual_kgraph_with_sketches_is_depth_distance():
+    """ContigInformation carries the contig's MinHash sketch (embedder.rs:96); with sketches the depth graph is
+    DepthDistance in full, metabat x (1 - min_jaccard) (embedder.rs:133-171)."""
+    n, s, k = 800, 4, 15
+    tnf, cov, _ = synth.knn_tables(n, s, seed=23)
+    hashes, offs = synth.sketches(n, seed=3, mean_size=30, share_frac=0.3)
+    g = host.build_mutual_kgraph(tnf, cov, keep_n_edges=3, n_neighbours=k, sketches=(hashes, offs), sketch_scale=0.1)
+    plain = host.build_mutual_kgraph(tnf, cov, keep_n_edges=3, n_neighbours=k)
+    oi, od = oracle.knn_depth_sketch(cov, hashes, offs, k, oracle.RUST, 0.1)
+    same = changed = 0
+    for node in range(n):
+        nodes, w = g.neighbours(node)
+        same += int(np.array_equal(nodes, oi[node]))
+        m = nodes == oi[node]
+        assert np.allclose(w[m], od[node][m].astype(np.float64), rtol=2.4e-7, atol=1e-15)
+        changed += int(not np.array_equal(nodes, plain.neighbours(node)[0]))
+    assert same > 0.98 * n and changed > 20
