@@ -73,6 +73,8 @@ void *rg_stream(rg_handle *h);
  *   "sym_block"        rows per block of the symmetric build (0 = 9472 = one wave of CTAs)
  *   "sym_chunk"        columns per evaluation launch of the symmetric build (0 = 4 blocks)
  *   "tnf_select_impl"  0 automatic (tcgen05 where its shape limits allow), 1 FP32 CUDA-core kernel
+ *   "exact_compact"    1 (default) the exhaustive pass collects the rows that pass its FP32 prefilter and evaluates them
+ *                      side by side; 0 = in place (A/B only)
  *   "certify"          1 (default) margin certificate + exhaustive f64 pass for uncertified rows; 0 = off (A/B only)
  *   "kprime_depth", "kprime_tnf"   candidate-list length override (0 = automatic; 48 (TNF only), 64, 128 or 256) */
 int32_t rg_set_option(rg_handle *h, const char *key, int64_t value);

@@ -248,6 +248,7 @@ rescore_kernel(const RescoreArgs a) {
 // flagged with bit 31 (their FP32 operands collide wholesale) and the TNF graphs evaluate every pair in f64.
 constexpr int XW = 8;
 constexpr int XPARTS = 16;     // a flagged row is split over up to 16 CTAs when few rows are flagged
+constexpr uint32_t XCAP = 4096; // rows per (flagged row, part) that may pass the FP32 prefilter and still be evaluated side by side
 
 struct ExactArgs {
     const double *data;
@@ -263,6 +264,7 @@ struct ExactArgs {
     const uint32_t *extra_idx;
     const uint32_t *extra_common;
     SketchArgs sk;
+    int compact;                   // 1: collect the rows that pass the prefilter and evaluate them side by side
     float *part_d;                 // scratch [gridDim.x][K]: sorted partial lists of split rows
     uint32_t *part_i;
     uint32_t *part_done;           // [gridDim.x] arrival counters of split rows (zero at launch)
@@ -295,7 +297,9 @@ exact_rows_kernel(const ExactArgs a) {
     float *ld = reinterpret_cast<float *>(qs + width);                                  // [XPARTS][K] (XW used per row part)
     uint32_t *li = reinterpret_cast<uint32_t *>(ld + XPARTS * K);
     ulonglong2 *q4 = reinterpret_cast<ulonglong2 *>(li + XPARTS * K);                   // [S][2] (DEPTH): {x,x,y,y},{z,z,w,w}
-    __shared__ uint32_t s_found, s_last;
+    uint32_t *cl_j = reinterpret_cast<uint32_t *>(q4 + 2 * S);                          // [XCAP] (DEPTH): rows that passed the prefilter
+    float *cl_d = reinterpret_cast<float *>(cl_j + XCAP);                               // [XCAP] their f64 distances (as f32)
+    __shared__ uint32_t s_found, s_last, s_cl;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t count = a.counters[0];
     if (count == 0) return;
@@ -316,7 +320,6 @@ exact_rows_kernel(const ExactArgs a) {
         if (WHICH == RG_GRAPH_DEPTH && a.extra_off) { eo = a.extra_off[grow]; ne = (uint32_t)(a.extra_off[grow + 1] - eo); }
         __syncthreads();
         for (uint32_t c = threadIdx.x; c < width; c += XW * 32) qs[c] = a.data[(uint64_t)grow * width + c];
-        for (int e = lane; e < K; e += 32) { ld[warp * K + e] = INFINITY; li[warp * K + e] = 0xffffffffu; }
         if (WHICH == RG_GRAPH_DEPTH && prefilter)
             for (uint32_t c = threadIdx.x; c < S; c += XW * 32) {
                 const float4 v = a.cov_t[((uint64_t)(grow / RG_TILE) * S + c) * RG_TILE + grow % RG_TILE];
@@ -324,43 +327,86 @@ exact_rows_kernel(const ExactArgs a) {
                 q4[2 * c + 1] = make_ulonglong2(mk(v.z, v.z).v, mk(v.w, v.w).v);
             }
         __syncthreads();
-        float thr = INFINITY;
         const uint32_t g_begin = (uint32_t)((uint64_t)n_groups * part / parts), g_end = (uint32_t)((uint64_t)n_groups * (part + 1) / parts);
-        for (uint32_t g = g_begin + warp; g < g_end; g += XW) {
-            const uint32_t j = g * 32 + lane;
-            bool want = j < n && j != grow;
-            if (WHICH == RG_GRAPH_DEPTH && prefilter) {
-                float acc0 = 0.f, cnt0 = 0.f, acc1 = 0.f, cnt1 = 0.f;
-                depthk::SignTrack unused;
-                const float4 *ref = a.cov_t + (uint64_t)g * S * RG_TILE + lane;
-                // two samples ahead in registers: the loop is a chain of ~150-cycle evaluations fed by global loads, and a
-                // CTA has only 8 warps to hide them behind
-                float4 b0 = ref[0], b1 = S > 1 ? ref[RG_TILE] : b0;
-                for (uint32_t smp = 0; smp < S; ++smp) {
-                    const float4 b = b0;
-                    b0 = b1;
-                    if (smp + 2 < S) b1 = ref[(size_t)(smp + 2) * RG_TILE];
-                    const ulonglong2 xy = q4[2 * smp], zw = q4[2 * smp + 1];
-                    depthk::depth_sample2<VARIANT, false>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc0, cnt0, acc1, cnt1, unused);
+        // Coverage graph with the FP32 prefilter: the rows that pass are rare and scattered, so evaluating them in place
+        // would run the ~60k-instruction f64 metric on one lane of a warp at a time.  Pass 0 therefore only COLLECTS the
+        // passing rows in shared memory; all 256 threads then evaluate them side by side and rank them by (distance,
+        // index).  If more than XCAP rows pass in this part (a cluster that size), pass 1 falls back to evaluating in
+        // place with the per-warp lists.
+        bool compact = WHICH == RG_GRAPH_DEPTH && prefilter && a.compact;
+        for (int pass = 0; pass < 2; ++pass) {
+            if (threadIdx.x == 0) s_cl = 0;
+            for (int e = lane; e < K; e += 32) { ld[warp * K + e] = INFINITY; li[warp * K + e] = 0xffffffffu; }
+            __syncthreads();
+            float thr = INFINITY;
+            for (uint32_t g = g_begin + warp; g < g_end; g += XW) {
+                const uint32_t j = g * 32 + lane;
+                bool want = j < n && j != grow;
+                if (WHICH == RG_GRAPH_DEPTH && prefilter) {
+                    float acc0 = 0.f, cnt0 = 0.f, acc1 = 0.f, cnt1 = 0.f;
+                    depthk::SignTrack unused;
+                    const float4 *ref = a.cov_t + (uint64_t)g * S * RG_TILE + lane;
+                    // two samples ahead in registers: the loop is a chain of ~150-cycle evaluations fed by global loads,
+                    // and a CTA has only 8 warps to hide them behind
+                    float4 b0 = ref[0], b1 = S > 1 ? ref[RG_TILE] : b0;
+                    for (uint32_t smp = 0; smp < S; ++smp) {
+                        const float4 b = b0;
+                        b0 = b1;
+                        if (smp + 2 < S) b1 = ref[(size_t)(smp + 2) * RG_TILE];
+                        const ulonglong2 xy = q4[2 * smp], zw = q4[2 * smp + 1];
+                        depthk::depth_sample2<VARIANT, false>(pk{xy.x}, pk{xy.y}, pk{zw.x}, pk{zw.y}, b, acc0, cnt0, acc1, cnt1, unused);
+                    }
+                    const float d32 = depthk::depth_finish<VARIANT>(acc0, cnt0);
+                    if (want && d32 > bound) {                 // not a neighbour by the FP32 value: keep only extra candidates
+                        bool joined;
+                        common_of(a.extra_idx, nullptr, eo, ne, j, &joined);
+                        want = joined;
+                    }
                 }
-                const float d32 = depthk::depth_finish<VARIANT>(acc0, cnt0);
-                if (want && d32 > bound) {                 // not a neighbour by the FP32 value: keep only extra candidates
-                    bool joined;
-                    common_of(a.extra_idx, nullptr, eo, ne, j, &joined);
-                    want = joined;
+                if (compact) {
+                    const unsigned m = __ballot_sync(0xffffffffu, want);
+                    if (m) {
+                        uint32_t base = 0;
+                        if (lane == 0) base = atomicAdd(&s_cl, (uint32_t)__popc(m));
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        const uint32_t pos = base + __popc(m & ((1u << lane) - 1u));
+                        if (want && pos < XCAP) cl_j[pos] = j;
+                    }
+                    continue;
                 }
+                float d = INFINITY;
+                if (want) {
+                    if (WHICH == RG_GRAPH_DEPTH) {
+                        float dm;
+                        const uint32_t common = a.sk.hash ? common_of(a.extra_idx, a.extra_common, eo, ne, j, nullptr) : 0u;
+                        d = depth_pair<VARIANT>(qs, a.data + (uint64_t)j * width, width, a.sk, grow, j, common, &dm);
+                    } else {
+                        d = pair_distance_f32<VARIANT, WHICH>(qs, a.data + (uint64_t)j * width, width);
+                    }
+                }
+                topk_offer<K>(ld + warp * K, li + warp * K, d, j, thr, lane);
             }
-            float d = INFINITY;
-            if (want) {
-                if (WHICH == RG_GRAPH_DEPTH) {
+            __syncthreads();
+            if (!compact) break;
+            const uint32_t L = s_cl;
+            if (L > XCAP) { compact = false; __syncthreads(); continue; }     // too many for the buffer: evaluate in place
+            if (WHICH == RG_GRAPH_DEPTH)
+                for (uint32_t e = threadIdx.x; e < L; e += XW * 32) {
+                    const uint32_t j = cl_j[e];
                     float dm;
                     const uint32_t common = a.sk.hash ? common_of(a.extra_idx, a.extra_common, eo, ne, j, nullptr) : 0u;
-                    d = depth_pair<VARIANT>(qs, a.data + (uint64_t)j * width, width, a.sk, grow, j, common, &dm);
-                } else {
-                    d = pair_distance_f32<VARIANT, WHICH>(qs, a.data + (uint64_t)j * width, width);
+                    cl_d[e] = depth_pair<VARIANT>(qs, a.data + (uint64_t)j * width, width, a.sk, grow, j, common, &dm);
                 }
+            __syncthreads();
+            for (uint32_t e = threadIdx.x; e < L; e += XW * 32) {             // the K best by (distance, index) -> list 0, sorted
+                const float d = cl_d[e];
+                const uint32_t j = cl_j[e];
+                uint32_t rank = 0;
+                for (uint32_t o = 0; o < L && rank < (uint32_t)K; ++o) rank += cl_d[o] < d || (cl_d[o] == d && cl_j[o] < j);
+                if (rank < (uint32_t)K) { ld[rank] = d; li[rank] = j; }
             }
-            topk_offer<K>(ld + warp * K, li + warp * K, d, j, thr, lane);
+            __syncthreads();
+            break;
         }
         if (threadIdx.x == 0) { s_found = 0; s_last = parts == 1; }
         if (parts > 1)                                      // this part's sorted list goes to scratch slot w
@@ -425,12 +471,13 @@ int32_t launch_exact(rg_handle *h, const double *data, uint32_t width, uint32_t 
                      uint32_t *idx, float *dist, uint32_t *nv) {
     const int K = k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256;
     const bool depth = WHICH == RG_GRAPH_DEPTH;
-    const size_t smem = (size_t)width * 8 + (size_t)XPARTS * K * 8 + (depth ? (size_t)(width / 2) * 32 : 0);
+    const size_t smem = (size_t)width * 8 + (size_t)XPARTS * K * 8 + (depth ? (size_t)(width / 2) * 32 + (size_t)XCAP * 8 : 0);
     const unsigned grid = (unsigned)h->sm_count * 2;
     // scratch of split rows: [grid][K] distances | [grid][K] indices | [grid] arrival counters
     RG_TRY(rg_reserve(h, h->exact_scratch, (size_t)grid * K * 8 + (size_t)grid * 4));
     RG_CUDA(h, cudaMemsetAsync((uint8_t *)h->exact_scratch.p + (size_t)grid * K * 8, 0, (size_t)grid * 4, h->stream));
     ExactArgs a{};
+    a.compact = h->opt_exact_compact;
     a.part_d = (float *)h->exact_scratch.p;
     a.part_i = (uint32_t *)h->exact_scratch.p + (size_t)grid * K;
     a.part_done = (uint32_t *)h->exact_scratch.p + (size_t)grid * K * 2;

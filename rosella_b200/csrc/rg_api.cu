@@ -126,6 +126,7 @@ int32_t rg_set_option(rg_handle *h, const char *key, int64_t value) {
     else if (k == "sym_block") { if (value < 0) return bad(); h->opt_sym_block = (uint64_t)value; }
     else if (k == "sym_chunk") { if (value < 0) return bad(); h->opt_sym_chunk = (uint64_t)value; }
     else if (k == "tnf_select_impl") { if (value < 0 || value > 1) return bad(); h->opt_tnf_fp32 = (int)value; }
+    else if (k == "exact_compact") { if (value < 0 || value > 1) return bad(); h->opt_exact_compact = (int)value; }
     else if (k == "certify") { if (value < 0 || value > 1) return bad(); h->opt_certify = (int)value; }
     else if (k == "kprime_depth") { if (value != 0 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_depth = (uint32_t)value; }
     else if (k == "kprime_tnf") { if (value != 0 && value != 48 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_tnf = (uint32_t)value; }

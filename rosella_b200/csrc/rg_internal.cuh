@@ -88,6 +88,7 @@ struct rg_handle {
     int opt_depth_build = 0;          // 0 = automatic, 1 = batch kernel, 2 = symmetric block build
     uint64_t opt_sym_block = 0, opt_sym_chunk = 0;   // rows per block / columns per launch of the symmetric build (0 = default)
     int opt_tnf_fp32 = 0;             // 1 = force the FP32 CUDA-core TNF select
+    int opt_exact_compact = 1;        // 0 = the exhaustive pass evaluates passing rows in place (A/B only)
     int opt_certify = 1;              // 0 = skip the margin certificate and the exhaustive pass (A/B measurements only)
     uint32_t opt_kprime_depth = 0, opt_kprime_tnf = 0;   // candidate-list override (test hook; 0 = automatic)
 
