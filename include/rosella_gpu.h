@@ -206,7 +206,9 @@ int32_t rg_comm_destroy(rg_handle *h);
 /* rows [*begin, *end) of an n-row graph that rank owns (whole 32-row tiles, sizes differ by at most one tile) */
 int32_t rg_comm_shard(uint64_t n, int32_t rank, int32_t world, uint64_t *begin, uint64_t *end);
 /* rg_knn_load across the communicator: only `root` reads its host tables (the others may pass NULL for a table the
- * root passes); the f64 tables travel by ncclBroadcast over NVLink instead of one PCIe upload per rank. */
+ * root passes); the f64 tables travel by ncclBroadcast over NVLink instead of one PCIe upload per rank.
+ * root = -1: every rank holds the same host tables (ranks in one process do): each rank uploads only ITS row shard over
+ * its own PCIe link and an in-place all-gather over NVLink completes the tables (rg_multi_* load this way). */
 int32_t rg_knn_load_dist(rg_handle *h, const double *tnf, const double *cov, uint64_t n, uint32_t d, uint32_t s,
                          uint32_t variant, int32_t root);
 /* Whole graph `which` of the loaded tables on all ranks.  Coverage graph: symmetric block build, every unordered

@@ -64,30 +64,50 @@ int32_t rg_knn_load_dist(rg_handle *h, const double *tnf, const double *cov, uin
                          uint32_t variant, int32_t root) {
     if (!h) return RG_ERR_INVALID;
     if (h->world <= 1 || !h->comm) return rg_knn_load(h, tnf, cov, n, d, s, variant);
-    if (root < 0 || root >= h->world) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_dist: root %d of %d", root, h->world);
+    if (root < -1 || root >= h->world) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_dist: root %d of %d", root, h->world);
     const NcclApi *api = rg_nccl(nullptr);
     RG_CUDA(h, cudaSetDevice(h->device));
     int32_t rc = ensure_events(h);
-    // which tables exist is the root's call
+    // which tables exist is the root's call (root == -1: every rank holds the same host tables, rank 0 speaks)
+    const int speaker = root < 0 ? 0 : root;
     int32_t have[2] = {tnf != nullptr, cov != nullptr};
     if (rc == RG_OK) rc = rg_reserve(h, h->dist_status, 4 * sizeof(int32_t));
     RG_TRY(rg_comm_agree(h, rc));
     int32_t *dev = (int32_t *)h->dist_status.p + 2;
     RG_CUDA(h, cudaMemcpyAsync(dev, have, sizeof(have), cudaMemcpyHostToDevice, h->stream));
-    RG_NCCL(h, api, Broadcast(dev, dev, 2, ncclInt32, root, (ncclComm_t)h->comm, h->stream));
+    RG_NCCL(h, api, Broadcast(dev, dev, 2, ncclInt32, speaker, (ncclComm_t)h->comm, h->stream));
     RG_CUDA(h, cudaMemcpyAsync(have, dev, sizeof(have), cudaMemcpyDeviceToHost, h->stream));
     RG_CUDA(h, cudaStreamSynchronize(h->stream));
     const bool has_tnf = have[0] != 0, has_cov = have[1] != 0;
-    RG_TRY(rg_comm_agree(h, rg_knn_load_begin(h, has_tnf, has_cov, n, d, s, variant)));
+    rc = rg_knn_load_begin(h, has_tnf, has_cov, n, d, s, variant);
+    if (rc == RG_OK && root < 0 && ((has_tnf && !tnf) || (has_cov && !cov)))
+        rc = rg_fail(h, RG_ERR_INVALID, "rg_knn_load_dist: root = -1 needs the host tables on every rank");
+    RG_TRY(rg_comm_agree(h, rc));
     RG_CUDA(h, cudaEventRecord(h->dist_ev[0], h->stream));
-    if (h->rank == root) {
-        if (has_tnf) RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-        if (has_cov) RG_CUDA(h, cudaMemcpyAsync(h->cov64.p, cov, n * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-        h->tm.h2d_bytes += (has_tnf ? n * d * 8 : 0) + (has_cov ? n * 2 * s * 8 : 0);
+    if (root >= 0) {
+        // one PCIe upload by the root, then NVLink
+        if (h->rank == root) {
+            if (has_tnf) RG_CUDA(h, cudaMemcpyAsync(h->tnf64.p, tnf, n * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            if (has_cov) RG_CUDA(h, cudaMemcpyAsync(h->cov64.p, cov, n * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            h->tm.h2d_bytes += (has_tnf ? n * d * 8 : 0) + (has_cov ? n * 2 * s * 8 : 0);
+        }
+        RG_CUDA(h, cudaEventRecord(h->dist_ev[1], h->stream));
+        if (has_tnf) RG_NCCL(h, api, Broadcast(h->tnf64.p, h->tnf64.p, n * d, ncclDouble, root, (ncclComm_t)h->comm, h->stream));
+        if (has_cov) RG_NCCL(h, api, Broadcast(h->cov64.p, h->cov64.p, n * 2 * s, ncclDouble, root, (ncclComm_t)h->comm, h->stream));
+    } else {
+        // every rank uploads ITS row shard over its own PCIe link (1 / world of the bytes each, all links at once), then
+        // an in-place all-gather over NVLink completes the tables everywhere
+        uint64_t qb, qe;
+        rg_shard(n, h->rank, h->world, &qb, &qe);
+        if (qe > qb) {
+            if (has_tnf) RG_CUDA(h, cudaMemcpyAsync((double *)h->tnf64.p + qb * d, tnf + qb * d, (qe - qb) * d * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            if (has_cov) RG_CUDA(h, cudaMemcpyAsync((double *)h->cov64.p + qb * 2 * s, cov + qb * 2 * s, (qe - qb) * 2 * s * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            h->tm.h2d_bytes += (qe - qb) * ((has_tnf ? d : 0) + (has_cov ? 2 * s : 0)) * 8;
+        }
+        RG_CUDA(h, cudaEventRecord(h->dist_ev[1], h->stream));
+        if (has_tnf) RG_TRY(all_gather_rows(h, api, h->tnf64.p, n, 2 * d));          // rows of d doubles = 2 d 4-byte elements
+        if (has_cov) RG_TRY(all_gather_rows(h, api, h->cov64.p, n, 4 * s));
     }
-    RG_CUDA(h, cudaEventRecord(h->dist_ev[1], h->stream));
-    if (has_tnf) RG_NCCL(h, api, Broadcast(h->tnf64.p, h->tnf64.p, n * d, ncclDouble, root, (ncclComm_t)h->comm, h->stream));
-    if (has_cov) RG_NCCL(h, api, Broadcast(h->cov64.p, h->cov64.p, n * 2 * s, ncclDouble, root, (ncclComm_t)h->comm, h->stream));
     RG_CUDA(h, cudaEventRecord(h->dist_ev[2], h->stream));
     RG_CUDA(h, cudaEventSynchronize(h->dist_ev[2]));
     h->dtm.load_h2d_ms = rg_elapsed(h->dist_ev[0], h->dist_ev[1]);

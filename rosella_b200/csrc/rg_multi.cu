@@ -128,7 +128,7 @@ int32_t rg_multi_knn_build(rg_multi *m, const double *tnf, const double *cov, ui
     if (want_tnf && (!tnf || !tnf_idx || !tnf_dist)) return bad("rg_multi_knn_build: TNF graph requested with a NULL pointer");
     if (want_depth && (!cov || !depth_idx || !depth_dist)) return bad("rg_multi_knn_build: depth graph requested with a NULL pointer");
     return run_all(m, [&](int, rg_handle *h) -> int32_t {
-        RG_TRY(rg_knn_load_dist(h, want_tnf ? tnf : nullptr, want_depth ? cov : nullptr, n, d, s, variant, 0));
+        RG_TRY(rg_knn_load_dist(h, want_tnf ? tnf : nullptr, want_depth ? cov : nullptr, n, d, s, variant, -1));
         if (want_depth) RG_TRY(rg_knn_build_dist(h, RG_GRAPH_DEPTH, k, 0, depth_idx, depth_dist));
         if (want_tnf) RG_TRY(rg_knn_build_dist(h, RG_GRAPH_TNF, k, 0, tnf_idx, tnf_dist));
         return RG_OK;
@@ -147,7 +147,7 @@ int32_t rg_multi_knn_build_sketched(rg_multi *m, const double *tnf, const double
     if (!want_depth || !cov || !depth_idx || !depth_dist || !offsets) return bad("rg_multi_knn_build_sketched: the depth graph, its table and the sketch offsets are required");
     if (want_tnf && (!tnf || !tnf_idx || !tnf_dist)) return bad("rg_multi_knn_build_sketched: TNF graph requested with a NULL pointer");
     return run_all(m, [&](int, rg_handle *h) -> int32_t {
-        RG_TRY(rg_knn_load_dist(h, want_tnf ? tnf : nullptr, cov, n, d, s, variant, 0));
+        RG_TRY(rg_knn_load_dist(h, want_tnf ? tnf : nullptr, cov, n, d, s, variant, -1));
         RG_TRY(rg_comm_agree(h, rg_knn_load_sketches(h, hashes, offsets, n, scale)));
         RG_TRY(rg_knn_build_dist(h, RG_GRAPH_DEPTH, k, 0, depth_idx, depth_dist));
         if (want_tnf) RG_TRY(rg_knn_build_dist(h, RG_GRAPH_TNF, k, 0, tnf_idx, tnf_dist));
@@ -164,7 +164,7 @@ int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *
         return RG_ERR_INVALID;
     }
     return run_all(m, [&](int i, rg_handle *h) -> int32_t {
-        RG_TRY(rg_knn_load_dist(h, tnf, cov, n, d, s, variant, 0));
+        RG_TRY(rg_knn_load_dist(h, tnf, cov, n, d, s, variant, -1));
         RG_TRY(rg_comm_agree(h, rg_reserve_list_cache(h, n, k)));
         // both graphs complete on every GPU (in-place all-gather); the filters then run on device 0
         RG_TRY(rg_knn_build_dist_dev(h, RG_GRAPH_DEPTH, k, 1, (uint32_t *)h->cache_di.p, (float *)h->cache_dd.p));
