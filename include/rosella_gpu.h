@@ -287,6 +287,17 @@ int32_t rg_graph_mutual(rg_handle *h, const uint32_t *idx, uint64_t n, uint32_t 
                         uint32_t keep_n_edges, uint8_t *keep);
 int32_t rg_graph_intersect(rg_handle *h, const uint32_t *base_idx, const uint32_t *other_idx,
                            uint64_t n, uint32_t k, uint32_t keep_n_edges, uint8_t *keep);
+/* rg_graph_mutual without any device allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and the same mask as rg_graph_mutual (host buffers), but the
+ * device staging (lists + mask) is a fixed `static __device__` array inside the library: at most
+ * RG_STATIC_MAX_EDGES = 2^20 edges (n * k), 5 MiB per GPU held until the process exits; larger inputs return
+ * RG_ERR_INVALID ("use rg_graph_mutual").  The call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine.  All calls on one GPU share the array: calls that overlap on the same GPU (other handles, threads or
+ * streams) race and must be serialised by the caller. */
+#define RG_STATIC_MAX_EDGES ((uint64_t)1 << 20)
+int32_t rg_graph_mutual_static(rg_handle *h, const uint32_t *idx, uint64_t n, uint32_t k,
+                               uint32_t keep_n_edges, uint8_t *keep);
 
 /* ------------------------------------------------------------------ instrumentation */
 typedef struct {

@@ -20,7 +20,7 @@ SYMBOLS = [
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
     "rg_knn_load", "rg_knn_load_sketches", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
-    "rg_graph_mutual", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
+    "rg_graph_mutual", "rg_graph_mutual_static", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
     "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat", "rg_condensed_euclidean", "rg_silhouette",
     "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
     "rg_knn_build_dist", "rg_get_dist_timings", "rg_get_dist_timings_of",
@@ -103,6 +103,7 @@ def load() -> C.CDLL:
         "rg_knn_build_mutual": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                             C.c_uint32, C.POINTER(C.c_uint64), u32p, f32p, C.POINTER(C.c_uint64), u32p]),
         "rg_graph_mutual": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
+        "rg_graph_mutual_static": (C.c_int32, [vp, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_graph_intersect": (C.c_int32, [vp, u32p, u32p, C.c_uint64, C.c_uint32, C.c_uint32, u8p]),
         "rg_get_timings": (C.c_int32, [vp, C.POINTER(Timings)]),
         "rg_knn_flagged_rows": (C.c_int32, [vp, u32p, f32p, f32p, C.c_uint64, C.POINTER(C.c_uint64)]),

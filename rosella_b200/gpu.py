@@ -339,6 +339,15 @@ class Context:
                                            _lib.ptr(keep, C.c_uint8)))
         return keep
 
+    def graph_mutual_static(self, idx, keep_n_edges: int):
+        """rg_graph_mutual_static: the same mask with the device staging in the library's fixed static array
+        (no device allocation inside the call; at most 2**20 edges)."""
+        idx = np.ascontiguousarray(idx, np.uint32)
+        keep = np.zeros(idx.shape, np.uint8)
+        self._chk(self.lib.rg_graph_mutual_static(self.h, _lib.ptr(idx, C.c_uint32), idx.shape[0], idx.shape[1],
+                                                  keep_n_edges, _lib.ptr(keep, C.c_uint8)))
+        return keep
+
     def graph_intersect(self, base, other, keep_n_edges: int):
         base = np.ascontiguousarray(base, np.uint32)
         other = np.ascontiguousarray(other, np.uint32)
