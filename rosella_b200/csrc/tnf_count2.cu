@@ -18,6 +18,9 @@
 //     cannot overflow; the flush sums the 128 bytes of a code with IDP.4A, folds the 256 raw codes to
 //     the 136 canonical bins (256 -> 136 LUT, tnf_host.cpp) into a CTA histogram, and that histogram
 //     goes to global memory only when the CTA moves on to another record.
+//   * the ASCII kernel classifies a unit of 32 bytes in registers (classify4: PRMT table look-ups keyed by byte & 7,
+//     one exact all-bases test per unit) and counts it like a packed word: 0.86 -> 2.26 Tbp/s (profiles/r2q_*); units
+//     with any other byte take the byte-by-byte path.
 // Integer work, bit-exact by construction; tests/test_gpu_tnf.py compares with the oracle.
 #include "rg_internal.cuh"
 #include "tnf_tables.h"
@@ -194,6 +197,23 @@ __device__ __forceinline__ void count_byte(uint8_t *__restrict__ cb, uint32_t tb
     }
 }
 
+// Classification of 4 raw bytes in registers (no class-table LDS): the low three bits of A/C/G/T/U (either case) are
+// 1 / 3 / 7 / 4 / 5 — distinct — so `byte & 7` selects, through PRMT, both the byte an A/C/G/T/U with those bits would
+// be (table EXP, 0xFF where none exists) and its 2-bit code (table COD).  byte ^ EXP[byte & 7] is 0x00 (upper case) or
+// 0x20 (lower case) exactly for the ten bytes needletail's normalize(false) turns into a base; OR-ing it over the unit
+// gives one exact all-bases test.  The selector nibbles come out pairwise swapped (b1, b0, b3, b2); the raw word is
+// permuted the same way for the compare and the packing multiply puts the codes back in order.
+// Returns the four codes in the TOP byte (first base lowest), junk below.
+__device__ __forceinline__ uint32_t classify4(uint32_t w, uint32_t &bad) {
+    const uint32_t v = w & 0x07070707u;
+    const uint32_t t = v * 0x1001u;                              // v | v << 12: byte 1 = (b1, b0), byte 3 = (b3, b2)
+    const uint32_t sel = __byte_perm(t, 0u, 0x0031u);
+    const uint32_t exp = __byte_perm(0x43FF41FFu, 0x47FF5554u, sel);
+    const uint32_t cod = __byte_perm(0x01000000u, 0x02000303u, sel);
+    bad |= __byte_perm(w, 0u, 0x2301u) ^ exp;
+    return cod * 0x04014010u;                                    // c0 << 24 | c1 << 26 | c2 << 28 | c3 << 30, disjoint partial products
+}
+
 __global__ void __launch_bounds__(T2, 6)
 tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restrict__ offsets,
                         const uint64_t *__restrict__ chunk_start, uint64_t n, uint64_t n_chunks,
@@ -224,21 +244,44 @@ tnf_count_ascii2_kernel(const uint8_t *__restrict__ seq, const uint64_t *__restr
         const uint64_t u0 = rb / SEG_BYTES + (chunk - chunk_start[cur.rec]) * UNIT_PER_CHUNK + tid;
         // depth-1 software pipeline of the two 16-byte loads of a unit
         uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+        uint32_t npw = 0;                                        // the 4 bytes before the unit
         if (u0 < u_end) {
             n0 = *reinterpret_cast<const uint4 *>(seq + u0 * SEG_BYTES);
             n1 = *reinterpret_cast<const uint4 *>(seq + u0 * SEG_BYTES + 16);
+            if (u0 > 0) npw = *reinterpret_cast<const uint32_t *>(seq + u0 * SEG_BYTES - 4);
         }
 #pragma unroll 1
         for (int i = 0; i < WPT; ++i) {
             const uint64_t u = u0 + (uint64_t)i * T2;
             if (u >= u_end) break;
             const uint4 q0 = n0, q1 = n1;
+            const uint32_t pw = npw;
             if (i + 1 < WPT && u + T2 < u_end) {
                 n0 = *reinterpret_cast<const uint4 *>(seq + (u + T2) * SEG_BYTES);
                 n1 = *reinterpret_cast<const uint4 *>(seq + (u + T2) * SEG_BYTES + 16);
+                npw = *reinterpret_cast<const uint32_t *>(seq + (u + T2) * SEG_BYTES - 4);
             }
             const uint64_t base = u * SEG_BYTES;
             const uint64_t p0 = max(base, rb), p1 = min(base + SEG_BYTES, re);
+            // Fast path: the unit and the 4 bytes before it lie inside the record and all 36 bytes are bases.  The 32
+            // codes are packed in registers and counted exactly like a word of the packed kernel: no class-table
+            // load, no rolling state, two ALU instructions and one ATOMS per base.
+            if (base >= rb + 4 && p1 == base + SEG_BYTES) {
+                uint32_t bad = 0, lo = 0, hi = 0;
+                hi = __funnelshift_l(classify4(q1.w, bad), hi, 8);
+                hi = __funnelshift_l(classify4(q1.z, bad), hi, 8);
+                hi = __funnelshift_l(classify4(q1.y, bad), hi, 8);
+                hi = __funnelshift_l(classify4(q1.x, bad), hi, 8);
+                lo = __funnelshift_l(classify4(q0.w, bad), lo, 8);
+                lo = __funnelshift_l(classify4(q0.z, bad), lo, 8);
+                lo = __funnelshift_l(classify4(q0.y, bad), lo, 8);
+                lo = __funnelshift_l(classify4(q0.x, bad), lo, 8);
+                const uint32_t pc = classify4(pw, bad) >> 26;    // the last 3 bases before the unit
+                if ((bad & 0xDFDFDFDFu) == 0u) {
+                    count_word(cb, tb, inc, ((uint64_t)hi << 32) | lo, 0xffffffffu, pc, 7u);
+                    continue;
+                }
+            }
             // rebuild the rolling state from the (up to) 3 kept bytes before p0
             uint8_t back[3];
             int nb = 0;

@@ -102,3 +102,29 @@ def test_chunk_boundaries_and_many_short_records(ctx):
         want = oracle.tnf_count(seq, offs, fast=True)
         c, nk, _ = ctx.tnf_count_ascii(seq2, offs2)
         assert np.array_equal(c, want[0]) and np.array_equal(nk, want[1])
+
+
+def test_every_byte_value_against_the_register_classifier(ctx):
+    """The ASCII kernel's fast path decides "all 36 bytes are bases" from `byte & 7` and two PRMT tables
+    (tnf_count2.cu, classify4): every one of the 256 byte values, at every position of a 32-byte unit and in the 4
+    bytes before it, inside otherwise clean sequence — against the faithful oracle.  Near misses of the test
+    ('@' 'B' 'F' '`' 'b' 'f' 'U' 'u', high-bit twins of the bases, control bytes with the same low bits) are all here."""
+    rng = np.random.default_rng(23)
+    alpha = np.frombuffer(b"ACGTacgtUu", np.uint8)
+    recs = []
+    for b in range(256):
+        r = alpha[rng.integers(0, len(alpha), 32 * 40 + int(rng.integers(0, 32)))].copy()
+        r[37 + 33 * np.arange(36)] = b                         # positions 37, 70, 103, ...: every offset mod 32
+        recs.append(bytes(r))
+    recs.append(bytes(alpha[rng.integers(0, len(alpha), 5000)]))   # clean: all units on the fast path
+    offs = np.zeros(len(recs) + 1, np.uint64)
+    offs[1:] = np.cumsum([len(r) for r in recs])
+    seq = np.frombuffer(b"".join(recs), np.uint8)
+    want = oracle.tnf_count(seq, offs)                          # the byte-by-byte restatement
+    _check(ctx, seq, offs, want)
+    for pad in (3, 29):                                         # other alignments of the records against the units
+        seq2 = np.concatenate([np.full(pad, ord("G"), np.uint8), seq])
+        offs2 = offs + np.uint64(pad); offs2[0] = 0
+        c, nk, _ = ctx.tnf_count_ascii(seq2, offs2)
+        w2 = oracle.tnf_count(seq2, offs2)
+        assert np.array_equal(c, w2[0]) and np.array_equal(nk, w2[1])
