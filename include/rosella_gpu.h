@@ -130,6 +130,21 @@ int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t
  * is not strictly increasing or one hash occurs in more than 4096 sketches. */
 int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, const uint64_t *offsets, uint64_t n, double scale);
 
+/* sketch_contigs (src/sketch/contig_sketcher.rs:47-92): finch's scaled MinHash of every record, the sketches
+ * rg_knn_load_sketches takes.  seq / offsets: the raw records exactly as for rg_tnf_count_ascii (normalize(false) of
+ * :59 happens on the device); kmer_length <= 32 (reference default 31), scale in (0, 1] (0.1), seed (42)
+ * (src/cli.rs:798-811).  Per record: every window of kmer_length A/C/G/T bases, the lexicographically smaller of the
+ * window and its reverse complement, MurmurHash3_x64_128(bytes, seed) first half; the sketch = the distinct hashes
+ * <= u64::MAX / (1/scale), padded with the next smallest distinct hashes up to kmers_to_sketch = (normalised length *
+ * scale) as usize entries (:65-71), ascending (finch ^0.6 ScaledSketcher restated: the crate is not part of the
+ * reference tree, see oracle/oracle_minhash.c).  sketch_offsets: n + 1 (host); n_valid_kmers (n, may be NULL): k-mers
+ * hashed per record (finch total_kmers, :76); *n_hashes (may be NULL) = sketch_offsets[n].  The hashes stay on the
+ * device until rg_sketch_fetch copies them (capacity in hashes, >= sketch_offsets[n]).  Records <= 2 GiB each.
+ * select_ms of rg_timings = device time of the call. */
+int32_t rg_sketch_contigs(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t kmer_length,
+                          double scale, uint64_t seed, uint64_t *sketch_offsets, uint64_t *n_valid_kmers, uint64_t *n_hashes);
+int32_t rg_sketch_fetch(rg_handle *h, uint64_t *hashes, uint64_t capacity);
+
 /* Exact top-k of query rows [q_begin, q_end) against all n loaded rows, self excluded, ascending
  * by (f32 distance, index).  idx/dist: (q_end-q_begin) x k; rows with fewer than k candidates are
  * padded with UINT32_MAX / +inf; n_valid (may be NULL) gets the count per row.

@@ -20,7 +20,7 @@ TNF, DEPTH, TNF_EUCLID = 0, 1, 2
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_tnf.c", "oracle_metrics.c", "oracle_knn.c", "oracle_sketch.c", "oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_tnf.c", "oracle_metrics.c", "oracle_knn.c", "oracle_sketch.c", "oracle_minhash.c", "oracle.h")]
     if force or not os.path.exists(_LIB_PATH) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs
     ):
@@ -38,6 +38,8 @@ def lib() -> C.CDLL:
             build()
         _lib = C.CDLL(_LIB_PATH)
         _lib.orc_normalize.restype = C.c_size_t
+        _lib.orc_sketch_max_hash.restype = C.c_uint64
+        _lib.orc_sketch_record.restype = C.c_uint64
         for f in ("orc_kmer_correlation", "orc_rho_flight", "orc_tnf_euclidean", "orc_metabat", "orc_min_jaccard", "orc_silhouette"):
             getattr(_lib, f).restype = C.c_double
         for f in ("orc_tnf_distance_f32", "orc_depth_distance_f32", "orc_sketch_distance_f32", "orc_depth_distance_sketch_f32"):
@@ -167,6 +169,31 @@ def build_mutual_kgraph(depth_idx, depth_dist, tnf_idx, keep_n_edges: int):
     offsets = np.zeros(n + 1, np.uint64)
     offsets[1:] = np.cumsum(counts)
     return offsets, f_idx[keep2], f_dist[keep2], np.where(counts == 0)[0].astype(np.uint32)
+
+
+def murmur3_x64_128(key: bytes, seed: int = 0) -> tuple[int, int]:
+    """MurmurHash3_x64_128 restated (oracle_minhash.c); finch's hash is the first half."""
+    buf = np.frombuffer(bytes(key), np.uint8) if len(key) else np.zeros(1, np.uint8)
+    out = np.zeros(2, np.uint64)
+    lib().orc_murmur3_x64_128(_p(buf, C.c_uint8), C.c_uint64(len(key)), C.c_uint64(seed), _p(out, C.c_uint64))
+    return int(out[0]), int(out[1])
+
+
+def sketch_max_hash(scale: float = 0.1) -> int:
+    return int(lib().orc_sketch_max_hash(C.c_double(scale)))
+
+
+def sketch_contigs(seq, offsets, k: int = 31, scale: float = 0.1, seed: int = 42):
+    """sketch_contigs (contig_sketcher.rs:47-92) -> (hashes u64[...], sk_offsets u64[n+1], n_valid_kmers u64[n], norm_len u64[n])."""
+    seq = np.ascontiguousarray(seq, np.uint8); offsets = np.ascontiguousarray(offsets, np.uint64)
+    n = len(offsets) - 1
+    sk_off = np.zeros(n + 1, np.uint64); nk = np.zeros(n, np.uint64); nl = np.zeros(n, np.uint64)
+    sp = _p(seq, C.c_uint8) if len(seq) else _p(np.zeros(1, np.uint8), C.c_uint8)
+    args = (sp, _p(offsets, C.c_uint64), C.c_uint64(n), C.c_uint32(k), C.c_double(scale), C.c_uint64(seed))
+    lib().orc_sketch_contigs(*args, _p(sk_off, C.c_uint64), None, _p(nk, C.c_uint64), _p(nl, C.c_uint64))
+    hashes = np.zeros(max(int(sk_off[-1]), 1), np.uint64)
+    lib().orc_sketch_contigs(*args, _p(sk_off, C.c_uint64), _p(hashes, C.c_uint64), None, None)
+    return hashes[: int(sk_off[-1])], sk_off, nk, nl
 
 
 def min_jaccard(q, r, scale: float = 0.1) -> float:

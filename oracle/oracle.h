@@ -91,6 +91,15 @@ void orc_knn_depth_sketch(const double *cov, uint64_t n, uint32_t width, int var
                           const uint64_t *offsets, double scale, const uint64_t *qrows, uint64_t nq, uint32_t k,
                           uint32_t *idx_out, float *dist_out, int threads);
 
+/* sketch_contigs (src/sketch/contig_sketcher.rs:47-92) with finch's scaled MinHash restated (oracle_minhash.c; the scheme
+ * is PARITY UNPINNED — finch is not under /root/reference; MurmurHash3_x64_128 is pinned against Appleby's source). */
+void orc_murmur3_x64_128(const uint8_t *key, uint64_t len, uint64_t seed, uint64_t out[2]);
+uint64_t orc_sketch_max_hash(double scale);
+uint64_t orc_sketch_record(const uint8_t *seq, uint64_t len, uint32_t k, double scale, uint64_t seed, uint64_t *out,
+                           uint64_t cap, uint64_t *n_valid_kmers, uint64_t *norm_len);
+void orc_sketch_contigs(const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t k, double scale, uint64_t seed,
+                        uint64_t *sk_offsets, uint64_t *hashes, uint64_t *n_valid_kmers, uint64_t *norm_len);
+
 void orc_coverage_distance_condensed(const double *cov, uint64_t n, uint32_t s, double *out, int threads);
 
 /* cluster_utils.rs:7-34 and :38-120 (silhouette with `a` over all other members, see oracle_sketch.c) */

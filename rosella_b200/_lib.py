@@ -18,7 +18,7 @@ SYMBOLS = [
     "rg_abi_version", "rg_create", "rg_destroy", "rg_last_error", "rg_sync", "rg_stream", "rg_set_option",
     "rg_tnf_canonical_kmers", "rg_tnf_count_ascii", "rg_tnf_packed_words", "rg_tnf_pack_host",
     "rg_tnf_count_packed", "rg_tnf_load_packed", "rg_tnf_load_ascii", "rg_tnf_count_resident", "rg_tnf_fetch",
-    "rg_knn_load", "rg_knn_load_sketches", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
+    "rg_knn_load", "rg_knn_load_sketches", "rg_sketch_contigs", "rg_sketch_fetch", "rg_knn_search", "rg_knn_search_dev", "rg_knn_build",
     "rg_knn_kprime", "rg_knn_depth_partial_dev", "rg_knn_depth_merge_dev", "rg_knn_build_mutual",
     "rg_graph_mutual", "rg_graph_mutual_static", "rg_graph_intersect", "rg_get_timings", "rg_knn_flagged_rows",
     "rg_knn_refilter", "rg_knn_build_subset", "rg_rank_stat", "rg_condensed_euclidean", "rg_silhouette",
@@ -93,6 +93,8 @@ def load() -> C.CDLL:
         "rg_tnf_fetch": (C.c_int32, [vp, u32p, u64p, f64p]),
         "rg_knn_load": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
         "rg_knn_load_sketches": (C.c_int32, [vp, u64p, u64p, C.c_uint64, C.c_double]),
+        "rg_sketch_contigs": (C.c_int32, [vp, u8p, u64p, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64, u64p, u64p, u64p]),
+        "rg_sketch_fetch": (C.c_int32, [vp, u64p, C.c_uint64]),
         "rg_knn_search": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, u32p, f32p, u32p]),
         "rg_knn_search_dev": (C.c_int32, [vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, vp, vp, vp]),
         "rg_knn_kprime": (C.c_uint32, [vp, C.c_uint32, C.c_uint32]),

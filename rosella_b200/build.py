@@ -19,7 +19,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall", "--
 # per-file extra flags: the f64 re-evaluation must not contract a*b+c into FMA (reference op order)
 EXTRA = {"knn_rescore.cu": ["-fmad=false"], "rank_stat.cu": ["-fmad=false"], "cluster_ops.cu": ["-fmad=false"]}
 SOURCES = ["rg_api.cu", "knn_transform.cu", "knn_depth2.cu", "knn_depth_sym.cu", "knn_tnf.cu", "knn_tnf_tc.cu", "knn_rescore.cu", "knn_exact.cu", "knn_search.cu",
-           "tnf_count.cu", "tnf_count2.cu", "tnf_api.cu", "graph_ops.cu", "graph_static.cu", "rg_comm.cu", "knn_dist.cu", "rg_multi.cu", "rank_stat.cu", "cluster_ops.cu", "tnf_host.cpp"]
+           "tnf_count.cu", "tnf_count2.cu", "tnf_api.cu", "graph_ops.cu", "graph_static.cu", "sketch.cu", "rg_comm.cu", "knn_dist.cu", "rg_multi.cu", "rank_stat.cu", "cluster_ops.cu", "tnf_host.cpp"]
 TOOLS = {"microbench.cu": "microbench", "microbench2.cu": "microbench2"}
 HEADERS = ["rg_internal.cuh", "rg_comm.h", "metric_f64.cuh", "pk.cuh", "knn_tnf_common.cuh", "knn_depth_common.cuh", "tnf_tables.h", os.path.join("..", "..", "include", "rosella_gpu.h")]
 

@@ -88,7 +88,7 @@ void rg_destroy(rg_handle *h) {
     DevBuf *bufs[] = {&h->tnf64, &h->cov64, &h->tnf_t, &h->tnf_norm, &h->tnf_mean, &h->tnf_hi, &h->tnf_lo, &h->cov_t, &h->err_flag,
                       &h->cand_d, &h->cand_i, &h->sym_d, &h->sym_t, &h->out_i, &h->out_d, &h->out_nv, &h->flag_list, &h->cert_ctr, &h->exact_scratch, &h->dist_pd, &h->dist_pi, &h->dist_rd, &h->dist_ri,
                       &h->dist_status, &h->cache_di, &h->cache_dd, &h->cache_ti, &h->cache_td,
-                      &h->row_flag, &h->extra_off, &h->extra_idx, &h->extra_common, &h->coll_pairs, &h->sk_hash, &h->sk_off, &h->codes, &h->valid,
+                      &h->row_flag, &h->extra_off, &h->extra_idx, &h->extra_common, &h->coll_pairs, &h->sk_hash, &h->sk_off, &h->skt_hash, &h->codes, &h->valid,
                       &h->woff, &h->ascii, &h->aoff, &h->counts, &h->nkmers, &h->freqs, &h->tnf_tables,
                       &h->chunk_start};
     for (DevBuf *b : bufs) rg_release(*b);

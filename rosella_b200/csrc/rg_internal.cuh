@@ -68,6 +68,10 @@ struct rg_handle {
     uint64_t sk_max_hash = 0;
     bool has_sketch = false;
 
+    // ---- MinHash sketching (sketch.cu): the sketches of the last rg_sketch_contigs, concatenated
+    DevBuf skt_hash;
+    uint64_t skt_total = 0, skt_redone = 0;   // hashes held; records redone with all their hashes (candidate threshold too low)
+
     // ---- multi-GPU (rg_comm.cu, knn_dist.cu): one handle = one rank of an NCCL communicator
     void *comm = nullptr;             // ncclComm_t (NCCL is dlopen'ed on first use; single-GPU callers never need it)
     int rank = 0, world = 1;

@@ -168,6 +168,22 @@ class Context:
         self._chk(self.lib.rg_knn_load_sketches(self.h, _lib.ptr(hashes, C.c_uint64), _lib.ptr(offsets, C.c_uint64),
                                                 len(offsets) - 1, scale))
 
+    def sketch_contigs(self, seq, offsets, kmer_length: int = 31, scale: float = 0.1, seed: int = 42):
+        """rg_sketch_contigs + rg_sketch_fetch (contig_sketcher.rs:47-92): finch's scaled MinHash per record
+        -> (hashes u64[...], sketch_offsets u64[n+1], n_valid_kmers u64[n])."""
+        seq = np.ascontiguousarray(seq, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        sk_off = np.zeros(n + 1, np.uint64)
+        nk = np.zeros(max(n, 1), np.uint64)
+        total = C.c_uint64(0)
+        sp = _lib.ptr(seq, C.c_uint8) if len(seq) else None
+        self._chk(self.lib.rg_sketch_contigs(self.h, sp, _lib.ptr(offsets, C.c_uint64), n, kmer_length, scale, seed,
+                                             _lib.ptr(sk_off, C.c_uint64), _lib.ptr(nk, C.c_uint64), C.byref(total)))
+        hashes = np.zeros(max(total.value, 1), np.uint64)
+        self._chk(self.lib.rg_sketch_fetch(self.h, _lib.ptr(hashes, C.c_uint64), len(hashes)))
+        return hashes[: total.value], sk_off, nk[:n]
+
     def knn_search(self, which: int, k: int, q_begin: int = 0, q_end: int | None = None):
         q_end = self._n if q_end is None else q_end
         nq = max(q_end - q_begin, 0)

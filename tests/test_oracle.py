@@ -243,3 +243,69 @@ def test_silhouette_restatement_matches_the_textbook_definition():
     lab2 = lab.copy(); lab2[:10] = -1; lab2[10] = 3
     score2, pp2 = oracle.silhouette(d, lab2, 4)
     assert (pp2[:10] == 0).all() and pp2[10] == 1.0 and abs(score2 - pp2.sum() / 120) < 1e-15
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# sketch_contigs (contig_sketcher.rs:47-92): finch's scaled MinHash restated in oracle/oracle_minhash.c
+
+def test_murmur3_x64_128_pinned_to_applebys_source(tmp_path):
+    """The hash function itself is pinned: known answer for b"hello", and every length 0..40 / several seeds against
+    Austin Appleby's MurmurHash3.cpp (public domain), which scikit-learn vendors on this image."""
+    import ctypes as C
+    import subprocess
+    assert oracle.murmur3_x64_128(b"hello", 0) == (0xcbd8a7b341bd9b02, 0x5b1e906a48ae1d19)
+    assert oracle.murmur3_x64_128(b"", 0) == (0, 0)
+    import sklearn
+    src = os.path.join(os.path.dirname(sklearn.__file__), "utils", "src", "MurmurHash3.cpp")
+    if not os.path.exists(src):
+        pytest.skip("no MurmurHash3.cpp on this image")
+    so = str(tmp_path / "libmm3.so")
+    subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-I", os.path.dirname(src), "-o", so, src])
+    ref = C.CDLL(so)
+    rng = np.random.default_rng(5)
+    for length in list(range(0, 41)) + [63, 64, 65, 255]:
+        key = bytes(rng.integers(0, 256, length, dtype=np.uint8))
+        for seed in (0, 42, 0xdeadbeef):
+            out = (C.c_uint64 * 2)()
+            ref.MurmurHash3_x64_128(key, length, C.c_uint32(seed), out)
+            assert oracle.murmur3_x64_128(key, seed) == (out[0], out[1]), (length, seed)
+
+
+def _revcomp(b: bytes) -> bytes:
+    return b.translate(bytes.maketrans(b"ACGTacgt", b"TGCAtgca"))[::-1]
+
+
+def test_sketch_contigs_restatement_properties():
+    rng = np.random.default_rng(9)
+    alpha = np.frombuffer(b"ACGT", np.uint8)
+    recs = [bytes(alpha[rng.integers(0, 4, n)]) for n in (5000, 1500, 40, 31, 30, 0)]
+    recs.append(b"ACGT" * 2000)                                   # 2 distinct canonical 31-mers: fewer than kmers_to_sketch
+    recs.append(recs[0][:2000] + b"N" * 500 + recs[0][2000:4000])
+    recs.append(_revcomp(recs[0]))
+    offs = np.zeros(len(recs) + 1, np.uint64); offs[1:] = np.cumsum([len(r) for r in recs])
+    seq = np.frombuffer(b"".join(recs), np.uint8)
+    h, so, nk, nl = oracle.sketch_contigs(seq, offs)
+    max_hash = oracle.sketch_max_hash(0.1)
+    assert max_hash == (2 ** 64 - 1) // 10
+    sk = [h[int(so[i]):int(so[i + 1])] for i in range(len(recs))]
+    for i, r in enumerate(recs):
+        assert nl[i] == len(r)
+        assert (np.diff(sk[i].astype(object)) > 0).all() if len(sk[i]) > 1 else True      # strictly ascending
+    assert nk[0] == 5000 - 30 and nk[3] == 1 and nk[4] == 0 and nk[5] == 0
+    # by hand for record 0: all canonical 31-mer hashes, distinct, ascending; <= max_hash, padded to 500
+    r = recs[0]
+    hs = set()
+    for p in range(len(r) - 30):
+        km = r[p:p + 31]
+        hs.add(oracle.murmur3_x64_128(min(km, _revcomp(km)), 42)[0])
+    hs = sorted(hs)
+    below = sum(1 for x in hs if x <= max_hash)
+    keep = below if below >= 500 else min(500, len(hs))
+    assert [int(x) for x in sk[0]] == hs[:keep]
+    # the reverse complement has the same canonical k-mers
+    assert np.array_equal(sk[0], sk[8])
+    # a record with 2 distinct canonical k-mers (ACGT is its own reverse complement) keeps both: kmers_to_sketch = 800
+    # cannot be reached
+    assert len(sk[6]) == 2 and nk[6] == 8000 - 30
+    # one k-mer: kept whatever its hash (1 <= kmers_to_sketch = 3)
+    assert len(sk[3]) == 1 and len(sk[4]) == 0
