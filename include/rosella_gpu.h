@@ -11,6 +11,7 @@
  *              src/kmers/kmer_counting.rs:366-414) and DepthDistance::eval :133-171
  *              (MetabatDistance::distance, src/coverage/coverage_calculator.rs:588-666)
  *   rg_graph_* compute what mutual_knn / intersect compute    src/graphs/nearest_neighbour_graph.rs:12-72
+ *   rg_sketch_* replace ContigSketcher::obtain_sketches        src/sketch/contig_sketcher.rs:47-92
  *
  * Conventions
  *   - plain pointers and sizes only; the caller owns every host buffer; the library never keeps
