@@ -128,7 +128,9 @@ int32_t rg_knn_load(rg_handle *h, const double *tnf, const double *cov, uint64_t
  * computes them on the reference side (src/sketch/contig_sketcher.rs:47-92; Sketch.hashes, sorted and unique), row i =
  * hashes[offsets[i] .. offsets[i+1]), offsets[0] = 0, n = the loaded rows; scale = SketchParams::Scaled.scale (0.1 by
  * default, 0 = unscaled).  Call after rg_knn_load (a new rg_knn_load drops the sketches).  RG_ERR_INVALID when a list
- * is not strictly increasing or one hash occurs in more than 4096 sketches. */
+ * is not strictly increasing or one hash occurs in more than 4096 sketches. 
+ * hashes == NULL (with offsets from rg_sketch_contigs): use the sketches that call left on this handle's device —
+ * no round trip through the host. */
 int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, const uint64_t *offsets, uint64_t n, double scale);
 
 /* sketch_contigs (src/sketch/contig_sketcher.rs:47-92): finch's scaled MinHash of every record, the sketches
@@ -141,7 +143,8 @@ int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, const uint64_
  * reference tree, see oracle/oracle_minhash.c).  sketch_offsets: n + 1 (host); n_valid_kmers (n, may be NULL): k-mers
  * hashed per record (finch total_kmers, :76); *n_hashes (may be NULL) = sketch_offsets[n].  The hashes stay on the
  * device until rg_sketch_fetch copies them (capacity in hashes, >= sketch_offsets[n]).  Records <= 2 GiB each.
- * select_ms of rg_timings = device time of the call. */
+ * rg_timings after the call: select_ms = device time of the whole call, of which h2d_ms = upload of the records,
+ * transform_ms = the two hash passes + scan, rescore_ms = the segmented sort (first pass of every slice). */
 int32_t rg_sketch_contigs(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t kmer_length,
                           double scale, uint64_t seed, uint64_t *sketch_offsets, uint64_t *n_valid_kmers, uint64_t *n_hashes);
 int32_t rg_sketch_fetch(rg_handle *h, uint64_t *hashes, uint64_t capacity);

@@ -309,7 +309,11 @@ extern "C" int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, co
     for (uint64_t r = 0; r < n; ++r)
         if (offsets[r + 1] < offsets[r]) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_sketches: offsets must be non-decreasing");
     const uint64_t total = offsets[n] - offsets[0];
-    if (total && !hashes) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_sketches: hashes is NULL");
+    // hashes == NULL: the sketches rg_sketch_contigs left on this handle (same total), copied device to device
+    const bool resident = total && !hashes && h->skt_hash.p && h->skt_total == total;
+    if (total && !hashes && !resident)
+        return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_sketches: hashes is NULL and the handle holds no sketches of %llu hashes from rg_sketch_contigs",
+                       (unsigned long long)total);
     if (offsets[0] != 0) return rg_fail(h, RG_ERR_INVALID, "rg_knn_load_sketches: offsets[0] must be 0");
     RG_CUDA(h, cudaSetDevice(h->device));
     h->has_sketch = false;
@@ -328,10 +332,11 @@ extern "C" int32_t rg_knn_load_sketches(rg_handle *h, const uint64_t *hashes, co
     XT(rg_reserve(h, h->sk_off, (n + 1) * 8));
     XT(rg_reserve(h, rows, (total ? total : 1) * 4)); XT(rg_reserve(h, keys2, (total ? total : 1) * 8)); XT(rg_reserve(h, rows2, (total ? total : 1) * 4));
     XT(rg_reserve(h, pairs, cap * 8)); XT(rg_reserve(h, ctr, 32)); XT(rg_reserve(h, er, n * 4)); XT(rg_reserve(h, nr, n * 4));
-    if (total) XC(cudaMemcpyAsync(h->sk_hash.p, hashes, total * 8, cudaMemcpyHostToDevice, h->stream));
+    if (total) XC(cudaMemcpyAsync(h->sk_hash.p, resident ? h->skt_hash.p : (const void *)hashes, total * 8,
+                                  resident ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h->stream));
     XC(cudaMemcpyAsync(h->sk_off.p, offsets, (n + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     XC(cudaMemsetAsync(ctr.p, 0, 32, h->stream));
-    h->tm.h2d_bytes += total * 8 + (n + 1) * 8;
+    h->tm.h2d_bytes += (resident ? 0 : total * 8) + (n + 1) * 8;
     unsigned long long *d_np = (unsigned long long *)ctr.p;
     uint32_t *d_flags = (uint32_t *)ctr.p + 2, *d_cnt = (uint32_t *)ctr.p + 4;
     if (total) {

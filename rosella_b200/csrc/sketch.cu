@@ -245,7 +245,8 @@ struct SliceCtx {
 };
 
 // steps 1-4 for the work items `ids` (NULL: all m records of the slice) with candidate threshold thr
-int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, uint64_t thr, bool with_counts, uint32_t *total_out) {
+int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, uint64_t thr, bool with_counts, uint32_t *total_out, bool *timed) {
+    *timed = false;
     rg_handle *h = c.h;
     int32_t rc = RG_OK;
     const uint32_t m = ids ? (uint32_t)ids->size() : c.m;
@@ -276,6 +277,7 @@ int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, u
     }
     SK_CUDA(cudaMemsetAsync((uint32_t *)P.seg_cnt.p + n_seg, 0, 4, h->stream));
     const unsigned grid = (n_seg + HT - 1) / HT;
+    cudaEventRecord(h->ev[5], h->stream);
     sketch_hash_kernel<false><<<grid, HT, 0, h->stream>>>(c.d_seq, c.d_off, d_ids, (const uint32_t *)P.seg_start.p, m, n_seg, c.k, c.seed,
                                                           thr, c.d_cls, (uint32_t *)P.seg_cnt.p, nullptr, nullptr,
                                                           with_counts ? c.d_nk : nullptr, with_counts ? c.d_nl : nullptr);
@@ -300,13 +302,16 @@ int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, u
     sketch_hash_kernel<true><<<grid, HT, 0, h->stream>>>(c.d_seq, c.d_off, d_ids, (const uint32_t *)P.seg_start.p, m, n_seg, c.k, c.seed, thr,
                                                          c.d_cls, nullptr, (const uint32_t *)P.seg_off.p, (uint64_t *)P.cand.p, nullptr, nullptr);
     SK_CUDA(cudaGetLastError());
+    cudaEventRecord(h->ev[6], h->stream);
     size_t sb = 0;
     SK_CUDA(cub::DeviceSegmentedSort::SortKeys(nullptr, sb, (const uint64_t *)P.cand.p, (uint64_t *)P.sorted.p, (int)total, (int)m,
                                                (const int *)P.begin.p, (const int *)P.begin.p + 1, h->stream));
     SK_TRY(rg_reserve(h, P.tmp, sb));
     SK_CUDA(cub::DeviceSegmentedSort::SortKeys(P.tmp.p, sb, (const uint64_t *)P.cand.p, (uint64_t *)P.sorted.p, (int)total, (int)m,
                                                (const int *)P.begin.p, (const int *)P.begin.p + 1, h->stream));
+    cudaEventRecord(h->ev[7], h->stream);
     h->tm.kernel_launches += 2;
+    *timed = true;
     return RG_OK;
 }
 
@@ -357,7 +362,11 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
         SK_TRY(rg_reserve(h, d_sc, (size_t)m * 4));
         SK_TRY(rg_reserve(h, d_sel, m));
         SK_TRY(rg_reserve(h, d_flag, m));
+        cudaEventRecord(h->ev[5], h->stream);
         if (bytes) SK_CUDA(cudaMemcpyAsync(d_seq.p, seq + sb, bytes, cudaMemcpyHostToDevice, h->stream));
+        cudaEventRecord(h->ev[6], h->stream);
+        SK_CUDA(cudaEventSynchronize(h->ev[6]));
+        h->tm.h2d_ms += rg_elapsed(h->ev[5], h->ev[6]);
         SK_CUDA(cudaMemcpyAsync(d_off.p, off.data(), ((size_t)m + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         SK_CUDA(cudaMemsetAsync(d_nk.p, 0, ((size_t)m + 1) * 8, h->stream));
         SK_CUDA(cudaMemsetAsync(d_nl.p, 0, ((size_t)m + 1) * 8, h->stream));
@@ -368,7 +377,8 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
         SliceCtx c{h, (const uint8_t *)d_seq.p, (const uint64_t *)d_off.p, off.data(), m, k, seed, (const uint8_t *)d_cls.p,
                    (unsigned long long *)d_nk.p, (unsigned long long *)d_nl.p};
         uint32_t total0 = 0, total1 = 0;
-        SK_TRY(run_pass(c, P0, nullptr, thr, true, &total0));
+        bool timed0 = false, timed1 = false;
+        SK_TRY(run_pass(c, P0, nullptr, thr, true, &total0, &timed0));
         const unsigned wgrid = (unsigned)(((uint64_t)m * 32 + 255) / 256);
         sketch_select_kernel<<<wgrid, 256, 0, h->stream>>>((const uint64_t *)P0.sorted.p, (const int *)P0.begin.p, nullptr, m, max_hash, thr, scale,
                                                            (const unsigned long long *)d_nl.p, (const unsigned long long *)d_nk.p,
@@ -379,13 +389,15 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
         SK_CUDA(cudaMemcpyAsync(&n_flag, d_nflag, 4, cudaMemcpyDeviceToHost, h->stream));
         SK_CUDA(cudaStreamSynchronize(h->stream));
         h->tm.kernel_launches += 1;
+        if (timed0) { h->tm.transform_ms += rg_elapsed(h->ev[5], h->ev[6]); h->tm.rescore_ms += rg_elapsed(h->ev[6], h->ev[7]); }
         if (n_flag) {
             std::vector<uint8_t> flag(m);
             SK_CUDA(cudaMemcpy(flag.data(), d_flag.p, m, cudaMemcpyDeviceToHost));
             std::vector<uint32_t> ids;
             ids.reserve(n_flag);
             for (uint32_t j = 0; j < m; ++j) if (flag[j]) ids.push_back(j);
-            SK_TRY(run_pass(c, P1, &ids, ~0ull, false, &total1));
+            SK_TRY(run_pass(c, P1, &ids, ~0ull, false, &total1, &timed1));
+            (void)timed1;
             const unsigned fgrid = (unsigned)(((uint64_t)ids.size() * 32 + 255) / 256);
             sketch_select_kernel<<<fgrid, 256, 0, h->stream>>>((const uint64_t *)P1.sorted.p, (const int *)P1.begin.p, (const uint32_t *)P1.rec_ids.p,
                                                                (uint32_t)ids.size(), max_hash, ~0ull, scale, (const unsigned long long *)d_nl.p,
@@ -441,11 +453,12 @@ extern "C" int32_t rg_sketch_contigs(rg_handle *h, const uint8_t *seq, const uin
     if (n == 0) return RG_OK;
     Pass P0, P1;
     DevBuf B[12];
+    h->tm.h2d_ms = h->tm.transform_ms = h->tm.rescore_ms = 0.0;
     cudaEventRecord(h->ev[3], h->stream);
     const int32_t rc = sketch_impl(h, seq, offsets, n, kmer_length, scale, seed, sketch_offsets, n_valid_kmers, P0, P1, B);
     cudaEventRecord(h->ev[4], h->stream);
     cudaStreamSynchronize(h->stream);
-    if (rc == RG_OK) { h->tm.select_ms = rg_elapsed(h->ev[3], h->ev[4]); h->tm.rescore_ms = 0.0; }
+    if (rc == RG_OK) h->tm.select_ms = rg_elapsed(h->ev[3], h->ev[4]);
     P0.release(); P1.release();
     for (DevBuf &b : B) rg_release(b);
     if (rc != RG_OK) { h->skt_total = 0; return rc; }

@@ -163,10 +163,12 @@ class Context:
 
     def knn_load_sketches(self, hashes, offsets, scale: float = 0.1):
         """MinHash sketches of the loaded rows (sorted u64 hash lists) -> RG_GRAPH_DEPTH becomes DepthDistance."""
-        hashes = np.ascontiguousarray(hashes, np.uint64)
         offsets = np.ascontiguousarray(offsets, np.uint64)
-        self._chk(self.lib.rg_knn_load_sketches(self.h, _lib.ptr(hashes, C.c_uint64), _lib.ptr(offsets, C.c_uint64),
-                                                len(offsets) - 1, scale))
+        hp = None                                    # None: the sketches the last sketch_contigs left on the device
+        if hashes is not None:
+            hashes = np.ascontiguousarray(hashes, np.uint64)
+            hp = _lib.ptr(hashes, C.c_uint64)
+        self._chk(self.lib.rg_knn_load_sketches(self.h, hp, _lib.ptr(offsets, C.c_uint64), len(offsets) - 1, scale))
 
     def sketch_contigs(self, seq, offsets, kmer_length: int = 31, scale: float = 0.1, seed: int = 42):
         """rg_sketch_contigs + rg_sketch_fetch (contig_sketcher.rs:47-92): finch's scaled MinHash per record

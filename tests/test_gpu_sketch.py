@@ -101,5 +101,12 @@ def test_gpu_sketches_feed_the_depth_graph(ctx):
     oi, od = oracle.knn_depth_sketch(cov, want_h, want_o, 10, oracle.RUST, 0.1)
     assert np.all(np.abs(dist - od) <= 2.4e-7 * np.abs(od) + 1e-15)
     assert (idx == oi).mean() > 0.999                            # ties at equal f32 distance may swap
+    # the same sketches taken straight from the device (hashes = None): no host round trip, same graph
+    ctx.knn_load(None, cov)
+    ctx.knn_load_sketches(None, o, 0.1)
+    idx2, dist2, _ = ctx.knn_search(gpu.GRAPH_DEPTH, 10)
+    assert np.array_equal(idx2, idx) and np.array_equal(dist2, dist)
+    with pytest.raises(gpu.RosellaGpuError, match="holds no sketches"):
+        ctx.knn_load_sketches(None, np.concatenate([o[:-1], o[-1:] + np.uint64(1)]), 0.1)
     plain_i, _, _ = (ctx.knn_load(None, cov), ctx.knn_search(gpu.GRAPH_DEPTH, 10))[1]
     assert (plain_i != idx).any(axis=1).sum() >= 5               # the planted shared stretches do change the graph
