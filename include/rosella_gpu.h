@@ -270,6 +270,11 @@ int32_t rg_multi_knn_build_mutual(rg_multi *m, const double *tnf, const double *
                                   uint32_t *neighbours, float *weights, uint64_t *n_disconnected, uint32_t *disconnected);
 int32_t rg_multi_tnf_count_ascii(rg_multi *m, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t *counts,
                                  uint64_t *n_kmers, double *freqs);
+/* rg_sketch_contigs / rg_sketch_fetch on all devices: contiguous ranges of records with equal bytes per device, no
+ * exchange; the arrays are the caller's, global (contig_sketcher.rs:47-92). */
+int32_t rg_multi_sketch_contigs(rg_multi *m, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t kmer_length,
+                                double scale, uint64_t seed, uint64_t *sketch_offsets, uint64_t *n_valid_kmers, uint64_t *n_hashes);
+int32_t rg_multi_sketch_fetch(rg_multi *m, uint64_t *hashes, uint64_t capacity);
 
 /* ------------------------------------------------------------------ flight's all-pairs rank statistic */
 /* ProfileDistanceEngine.makeRankStat (flight/flight/distance.py:92-108, as flight/flight/rosella/rosella.py:337-350

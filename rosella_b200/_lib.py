@@ -25,7 +25,7 @@ SYMBOLS = [
     "rg_comm_unique_id", "rg_comm_init", "rg_comm_destroy", "rg_comm_shard", "rg_knn_load_dist", "rg_knn_build_dist_dev",
     "rg_knn_build_dist", "rg_get_dist_timings", "rg_get_dist_timings_of",
     "rg_multi_create", "rg_multi_destroy", "rg_multi_last_error", "rg_multi_size", "rg_multi_handle", "rg_multi_knn_build", "rg_multi_knn_build_sketched",
-    "rg_multi_knn_build_mutual", "rg_multi_tnf_count_ascii",
+    "rg_multi_knn_build_mutual", "rg_multi_tnf_count_ascii", "rg_multi_sketch_contigs", "rg_multi_sketch_fetch",
 ]
 
 
@@ -136,6 +136,8 @@ def load() -> C.CDLL:
         "rg_multi_knn_build_mutual": (C.c_int32, [vp, f64p, f64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                                   C.c_uint32, u64p, u32p, f32p, u64p, u32p]),
         "rg_multi_tnf_count_ascii": (C.c_int32, [vp, u8p, u64p, C.c_uint64, u32p, u64p, f64p]),
+        "rg_multi_sketch_contigs": (C.c_int32, [vp, u8p, u64p, C.c_uint64, C.c_uint32, C.c_double, C.c_uint64, u64p, u64p, u64p]),
+        "rg_multi_sketch_fetch": (C.c_int32, [vp, u64p, C.c_uint64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -19,6 +19,7 @@ int32_t rg_reserve_list_cache(rg_handle *h, uint64_t n, uint32_t k);
 struct rg_multi {
     std::vector<rg_handle *> hs;
     std::string err;
+    std::vector<uint64_t> skt_base;      // rg_multi_sketch_contigs: first hash of device i in the concatenated sketches
 };
 
 namespace {
@@ -203,6 +204,63 @@ int32_t rg_multi_tnf_count_ascii(rg_multi *m, const uint8_t *seq, const uint64_t
         for (uint64_t r = a; r <= b; ++r) local[r - a] = offsets[r] - base;
         return rg_tnf_count_ascii(h, seq + base, local.data(), b - a, counts + a * RG_NBINS, n_kmers + a,
                                   freqs ? freqs + a * RG_NBINS : nullptr);
+    });
+}
+
+// sketch_contigs on all devices: contiguous ranges of records with equal bytes per device (the split of
+// rg_multi_tnf_count_ascii), every device sketches its range from its own upload; no exchange.  The hashes stay on the
+// devices until rg_multi_sketch_fetch copies every device's slab to its place in the caller's array.
+int32_t rg_multi_sketch_contigs(rg_multi *m, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t kmer_length,
+                                double scale, uint64_t seed, uint64_t *sketch_offsets, uint64_t *n_valid_kmers, uint64_t *n_hashes) {
+    if (!m) return RG_ERR_INVALID;
+    if (!offsets || !sketch_offsets) {
+        m->err = "rg_multi_sketch_contigs: NULL pointer";
+        return RG_ERR_INVALID;
+    }
+    const int nd = (int)m->hs.size();
+    std::vector<uint64_t> cut(nd + 1, 0), totals(nd, 0);
+    const uint64_t base0 = n ? offsets[0] : 0, total = n ? offsets[n] - base0 : 0;
+    for (int i = 1; i < nd; ++i) {
+        const uint64_t target = base0 + total / nd * i;
+        cut[i] = std::max<uint64_t>(cut[i - 1], (uint64_t)(std::lower_bound(offsets, offsets + n + 1, target) - offsets));
+        if (cut[i] > n) cut[i] = n;
+    }
+    cut[nd] = n;
+    m->skt_base.assign(nd + 1, 0);
+    sketch_offsets[0] = 0;
+    const int32_t rc = run_all(m, [&](int i, rg_handle *h) -> int32_t {
+        const uint64_t a = cut[i], b = cut[i + 1];
+        std::vector<uint64_t> local(b - a + 1);
+        for (uint64_t r = a; r <= b; ++r) local[r - a] = offsets[r] - offsets[a];
+        std::vector<uint64_t> sk(b - a + 1, 0);
+        RG_TRY(rg_sketch_contigs(h, seq ? seq + offsets[a] : nullptr, local.data(), b - a, kmer_length, scale, seed, sk.data(),
+                                 n_valid_kmers ? n_valid_kmers + a : nullptr, &totals[i]));
+        for (uint64_t r = a + 1; r <= b; ++r) sketch_offsets[r] = sk[r - a];      // relative to the device's slab for now
+        return RG_OK;
+    });
+    if (rc != RG_OK) return rc;
+    for (int i = 0; i < nd; ++i) {
+        m->skt_base[i + 1] = m->skt_base[i] + totals[i];
+        for (uint64_t r = cut[i] + 1; r <= cut[i + 1]; ++r) sketch_offsets[r] += m->skt_base[i];
+    }
+    if (n_hashes) *n_hashes = m->skt_base[nd];
+    return RG_OK;
+}
+
+int32_t rg_multi_sketch_fetch(rg_multi *m, uint64_t *hashes, uint64_t capacity) {
+    if (!m) return RG_ERR_INVALID;
+    const int nd = (int)m->hs.size();
+    if ((int)m->skt_base.size() != nd + 1) {
+        m->err = "rg_multi_sketch_fetch: call rg_multi_sketch_contigs first";
+        return RG_ERR_STATE;
+    }
+    if (m->skt_base[nd] && (!hashes || capacity < m->skt_base[nd])) {
+        m->err = "rg_multi_sketch_fetch: room for " + std::to_string(capacity) + " hashes, the sketches hold " + std::to_string(m->skt_base[nd]);
+        return RG_ERR_INVALID;
+    }
+    return run_all(m, [&](int i, rg_handle *h) -> int32_t {
+        const uint64_t cnt = m->skt_base[i + 1] - m->skt_base[i];
+        return cnt ? rg_sketch_fetch(h, hashes + m->skt_base[i], cnt) : (int32_t)RG_OK;
     });
 }
 

@@ -456,3 +456,18 @@ class Multi:
                                                     _lib.ptr(counts, C.c_uint32), _lib.ptr(nk, C.c_uint64),
                                                     _lib.ptr(freqs, C.c_double)))
         return counts, nk, freqs
+
+    def sketch_contigs(self, seq, offsets, kmer_length: int = 31, scale: float = 0.1, seed: int = 42):
+        """rg_multi_sketch_contigs + rg_multi_sketch_fetch -> (hashes, sketch_offsets, n_valid_kmers)."""
+        seq = np.ascontiguousarray(seq, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        n = len(offsets) - 1
+        sk_off = np.zeros(n + 1, np.uint64)
+        nk = np.zeros(max(n, 1), np.uint64)
+        total = C.c_uint64(0)
+        self._chk(self.lib.rg_multi_sketch_contigs(self.m, _lib.ptr(seq, C.c_uint8) if len(seq) else None, _lib.ptr(offsets, C.c_uint64),
+                                                   n, kmer_length, scale, seed, _lib.ptr(sk_off, C.c_uint64),
+                                                   _lib.ptr(nk, C.c_uint64), C.byref(total)))
+        hashes = np.zeros(max(total.value, 1), np.uint64)
+        self._chk(self.lib.rg_multi_sketch_fetch(self.m, _lib.ptr(hashes, C.c_uint64), len(hashes)))
+        return hashes[: total.value], sk_off, nk[:n]

@@ -44,6 +44,10 @@ def load() -> C.CDLL:
         "rh_fastx_id": (C.c_char_p, [vp, sz]), "rh_fastx_seq": (C.POINTER(C.c_uint8), [vp]),
         "rh_fastx_offsets": (C.POINTER(C.c_uint64), [vp]),
         "rh_count_kmers": (vp, [C.c_int, C.c_char_p, C.c_char_p, C.c_int]),
+        "rh_sketch_contigs": (vp, [C.c_int, C.c_char_p, sz, sz, C.c_double, C.c_uint64]),
+        "rh_sketches_free": (None, [vp]), "rh_sketches_n": (sz, [vp]), "rh_sketches_name": (C.c_char_p, [vp, sz]),
+        "rh_sketches_offsets": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_hashes": (C.POINTER(C.c_uint64), [vp]),
+        "rh_sketches_num_valid_kmers": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_seq_length": (C.POINTER(C.c_uint64), [vp]),
         "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_double]),
         "rh_graph_free": (None, [vp]), "rh_graph_nb_nodes": (sz, [vp]), "rh_graph_max_nbng": (sz, [vp]),
@@ -163,6 +167,27 @@ def parse_fastx_file(path: str):
 def count_kmers(assembly: str, output_directory: str, no_flight: bool = False, device: int = 0) -> KmerFrequencyTable:
     """count_kmers(m, n_contigs) (kmer_counting.rs:13-16) on the GPU"""
     return KmerFrequencyTable(load().rh_count_kmers(device, assembly.encode(), output_directory.encode(), int(no_flight)))
+
+
+def sketch_contigs(assembly: str, min_contig_size: int = 1500, kmer_size: int = 31, sketch_scale: float = 0.1, seed: int = 42,
+                   device: int = 0):
+    """sketch_contigs(m) (contig_sketcher.rs:11-92) on the GPU
+    -> (contig_names, hashes u64[...], offsets u64[n+1], num_valid_kmers u64[n], seq_length u64[n])"""
+    lib = load()
+    h = lib.rh_sketch_contigs(device, assembly.encode(), min_contig_size, kmer_size, sketch_scale, seed)
+    if not h:
+        raise _err()
+    try:
+        n = lib.rh_sketches_n(h)
+        names = [lib.rh_sketches_name(h, i).decode() for i in range(n)]
+        offs = np.ctypeslib.as_array(lib.rh_sketches_offsets(h), (n + 1,)).copy()
+        total = int(offs[-1])
+        hashes = np.ctypeslib.as_array(lib.rh_sketches_hashes(h), (total,)).copy() if total else np.zeros(0, np.uint64)
+        nk = np.ctypeslib.as_array(lib.rh_sketches_num_valid_kmers(h), (n,)).copy() if n else np.zeros(0, np.uint64)
+        sl = np.ctypeslib.as_array(lib.rh_sketches_seq_length(h), (n,)).copy() if n else np.zeros(0, np.uint64)
+    finally:
+        lib.rh_sketches_free(h)
+    return names, hashes, offs, nk, sl
 
 
 class KGraphResult:

@@ -106,6 +106,36 @@ KmerFrequencyTable *rh_count_kmers(int device, const char *assembly, const char 
     return t;
 }
 
+struct rh_sketches {
+    ContigSketchResult r;
+    std::vector<uint64_t> offsets, hashes, num_valid_kmers, seq_length;
+};
+rh_sketches *rh_sketch_contigs(int device, const char *assembly, size_t min_contig_size, size_t kmer_size, double scale, uint64_t seed) {
+    rh_sketches *out = nullptr;
+    if (guard([&] {
+            Gpu gpu(device);
+            SketchContigsArgs m{assembly, min_contig_size, SketchSettings{kmer_size, scale, seed}};
+            auto p = std::make_unique<rh_sketches>();
+            p->r = sketch_contigs(gpu, m);
+            p->offsets.push_back(0);
+            for (const Sketch &s : p->r.contig_sketches) {
+                p->hashes.insert(p->hashes.end(), s.hashes.begin(), s.hashes.end());
+                p->offsets.push_back(p->hashes.size());
+                p->num_valid_kmers.push_back(s.num_valid_kmers);
+                p->seq_length.push_back(s.seq_length);
+            }
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
+void rh_sketches_free(rh_sketches *s) { delete s; }
+size_t rh_sketches_n(const rh_sketches *s) { return s->r.contig_names.size(); }
+const char *rh_sketches_name(const rh_sketches *s, size_t i) { return s->r.contig_names.at(i).c_str(); }
+const uint64_t *rh_sketches_offsets(const rh_sketches *s) { return s->offsets.data(); }
+const uint64_t *rh_sketches_hashes(const rh_sketches *s) { return s->hashes.data(); }
+const uint64_t *rh_sketches_num_valid_kmers(const rh_sketches *s) { return s->num_valid_kmers.data(); }
+const uint64_t *rh_sketches_seq_length(const rh_sketches *s) { return s->seq_length.data(); }
+
 // sketch_hashes / sketch_offsets (n + 1 entries) may be NULL: no sketches
 rh_graph *rh_build_mutual_kgraph(int device, const double *tnf, size_t d, const double *cov, size_t c, size_t n,
                                  size_t keep_n_edges, size_t n_neighbours, size_t max_layers, size_t ef_construction,

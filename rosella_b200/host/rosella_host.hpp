@@ -5,6 +5,7 @@
 //   count_kmers / KmerCounter::run      src/kmers/kmer_counting.rs:13-16, :41-123
 //   KmerFrequencyTable                  src/kmers/kmer_counting.rs:211-360
 //   ContigInformation, EmbedderEngine   src/embedding/embedder.rs:15-104
+//   sketch_contigs, ContigSketchResult  src/sketch/contig_sketcher.rs:11-92, :152-176
 //   KGraph / OutEdge                    annembed::fromhnsw::kgraph (third party; the subset the path uses)
 //   mutual_knn / intersect              src/graphs/nearest_neighbour_graph.rs:12-72
 //   RecoverEngine::build_mutual_kgraph  src/recover/recover_engine.rs:510-519 (k clamp)
@@ -78,6 +79,36 @@ struct CountKmersArgs {          // the two clap arguments KmerCounter::new read
 // count_kmers(m, n_contigs) (:13-16): reuses <out>/kmer_frequencies.tsv when present (:46-50), otherwise
 // reads the assembly, counts on the GPU, writes the table and reads it back (:117-120)
 KmerFrequencyTable count_kmers(Gpu &gpu, const CountKmersArgs &m, std::optional<size_t> n_contigs, bool no_flight);
+
+// ------------------------------------------------------------------ sketching (src/sketch/contig_sketcher.rs)
+struct SketchSettings {           // :133-150; clap defaults src/cli.rs:798-811
+    size_t kmer_size = 31;
+    double sketch_scale = 0.1;
+    uint64_t seed = 42;
+};
+// finch::serialization::Sketch, the fields contig_sketcher.rs:80-88 fills and the path reads.  hashes = KmerCount.hash
+// of to_vec(): ascending, distinct (the k-mer bytes and counts of KmerCount are not produced; SketchDistance reads
+// the hash only, sketch_distances.rs:61-126).
+struct Sketch {
+    std::string name;
+    uint64_t seq_length = 0;        // total_bases
+    uint64_t num_valid_kmers = 0;   // total_kmers
+    std::vector<uint64_t> hashes;
+    SketchSettings sketch_params;   // SketchParams::Scaled { kmer_length, scale, hash_seed }
+    size_t kmers_to_sketch = 0;     //                      { kmers_to_sketch } (:65)
+};
+struct ContigSketchResult {       // :152-176
+    std::vector<std::string> contig_names;
+    std::vector<Sketch> contig_sketches;
+    void filter_by_index(const std::set<size_t> &indices_to_remove);
+};
+struct SketchContigsArgs {        // the clap arguments ContigSketcher::new reads (:23-26)
+    std::string assembly;
+    size_t min_contig_size = 1500;
+    SketchSettings sketch_settings;
+};
+// sketch_contigs(m) (:11-14): ContigSketcher::run -> obtain_sketches (:47-92), all records in one device call
+ContigSketchResult sketch_contigs(Gpu &gpu, const SketchContigsArgs &m);
 
 // ------------------------------------------------------------------ graph types (annembed KGraph subset)
 struct OutEdge {

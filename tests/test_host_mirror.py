@@ -190,6 +190,27 @@ def test_count_kmers_matches_the_oracle_and_reuses_the_table(tmp_path):
 
 
 @pytest.mark.gpu
+def test_sketch_contigs_matches_the_oracle(tmp_path):
+    """sketch_contigs (contig_sketcher.rs:11-92): FASTA (60-column lines) -> min_contig_size filter -> one sketch per
+    record, against the oracle's restatement of finch on the records that pass the filter."""
+    seq, offs = synth.contigs(300_000, threads=2, min_len=400, max_len=9000)
+    ids = [f"k141_{i} len={int(offs[i + 1] - offs[i])}" for i in range(len(offs) - 1)]
+    seqs = [bytes(seq[int(offs[i]):int(offs[i + 1])]).decode() for i in range(len(ids))]
+    fa = str(tmp_path / "assembly.fna")
+    _write_fasta(fa, ids, seqs)
+    names, hashes, so, nk, sl = host.sketch_contigs(fa, min_contig_size=1500)
+    got_ids, raw, roffs = host.parse_fastx_file(fa)                 # the raw records (with their line breaks)
+    keep = [i for i in range(len(got_ids)) if int(roffs[i + 1] - roffs[i]) >= 1500]
+    assert names == [got_ids[i] for i in keep] and 0 < len(keep) < len(ids)
+    recs = [bytes(raw[int(roffs[i]):int(roffs[i + 1])]) for i in keep]
+    koffs = np.zeros(len(recs) + 1, np.uint64); koffs[1:] = np.cumsum([len(r) for r in recs])
+    wh, wo, wnk, wnl = oracle.sketch_contigs(np.frombuffer(b"".join(recs), np.uint8), koffs)
+    assert np.array_equal(so, wo) and np.array_equal(hashes, wh) and np.array_equal(nk, wnk) and np.array_equal(sl, wnl)
+    with pytest.raises(host.HostError):
+        host.sketch_contigs(str(tmp_path / "missing.fna"))
+
+
+@pytest.mark.gpu
 def test_build_mutual_kgraph_matches_the_exhaustive_oracle():
     """EmbedderEngine::build_mutual_kgraph (embedder.rs:31-86): the returned graph is the depth kNN graph (the
     reference drops the intersect / mutual results, nearest_neighbour_graph.rs:33,:70); apply_filters applies them."""

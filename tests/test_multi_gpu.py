@@ -41,6 +41,8 @@ def test_multi_with_one_device_equals_the_single_handle(ctx):
             assert np.array_equal(a, b)
         mc, mnk, mf = m.tnf_count_ascii(seq, offs)
         assert np.array_equal(mc, c) and np.array_equal(mnk, nk) and np.array_equal(mf, f, equal_nan=True)
+        for a, b in zip(m.sketch_contigs(seq, offs), ctx.sketch_contigs(seq, offs)):
+            assert np.array_equal(a, b)
 
 
 @pytest.mark.gpu
@@ -109,6 +111,8 @@ def test_multi_two_devices_equal_one(ctx, n, s, k):
         c, nk, f = ctx.tnf_count_ascii(seq, offs)
         mc, mnk, mf = m.tnf_count_ascii(seq, offs)
         assert np.array_equal(mc, c) and np.array_equal(mnk, nk) and np.array_equal(mf, f, equal_nan=True)
+        for a, b in zip(m.sketch_contigs(seq, offs), ctx.sketch_contigs(seq, offs)):      # per-device ranges, same sketches
+            assert np.array_equal(a, b)
     # one failing rank must fail the call on every rank instead of hanging the others
     bad = cov.copy(); bad[5, 1] = np.nan
     with gpu.Multi([0, 1]) as m:
