@@ -77,14 +77,43 @@ def run(ctx, total_bp: int, steps: int, warmup: int, hbm_gbs: float, threads: in
             "frac": link_bytes / float(np.mean(e2e)) / 1e9 / best, "bytes_over_the_link_per_call": link_bytes,
             "peak_source": "pinned 1 GiB host->device copy (one cudaMemcpyAsync), best of 4, measured in this run"}
     del probe, dst
+    ascii_ms = float(np.mean(ms_a))
+    ascii_bytes = bases + n * (136 * 4 + 8 + 8)
+    # ---- MinHash sketching (sketch_contigs, contig_sketcher.rs:47-92) of a <= 2 Gbp prefix of the same pinned records:
+    # rg_sketch_contigs + rg_sketch_fetch through the C ABI; device time and its phases from the library's CUDA events
+    sketch = None
+    try:
+        ks = int(np.searchsorted(offs, np.uint64(min(bases, 2_000_000_000)), side="right")) - 1
+        ks = max(ks, 1)
+        sb = int(offs[ks])
+        ctx.sketch_contigs(seq_pin[: int(offs[min(ks, 20)])], offs[: min(ks, 20) + 1])
+        best_w, best_tm, n_h = None, None, 0
+        for _ in range(2):
+            t = time.perf_counter()
+            h, so, _ = ctx.sketch_contigs(seq_pin[:sb], offs[: ks + 1])
+            w = time.perf_counter() - t
+            if best_w is None or w < best_w:
+                best_w, best_tm, n_h = w, ctx.timings(), int(so[-1])
+            del h
+        sketch = {"bases": sb, "contigs": ks, "hashes": n_h, "kmer_length": 31, "scale": 0.1, "seed": 42,
+                  "device_ms": best_tm["select_ms"], "upload_ms": best_tm["h2d_ms"], "hash_ms": best_tm["transform_ms"],
+                  "sort_ms": best_tm["rescore_ms"], "gbp_per_s_device": sb / (best_tm["select_ms"] * 1e-3) / 1e9,
+                  "e2e_s": best_w, "gbp_per_s_e2e": sb / best_w / 1e9,
+                  "what": "host ASCII (pinned) -> sketches in pageable host memory, rg_sketch_contigs + rg_sketch_fetch"}
+    except Exception as exc:  # the bench line must survive a failure of this side leg
+        sketch = {"error": repr(exc)}
     return {
         "value": bases / (kern_ms * 1e-3) / 1e9, "unit": "Gbp/s", "bases": bases, "contigs": n,
-        "kernel_ms": kern_ms, "ascii_kernel_ms": float(np.mean(ms_a)),
-        "ascii_kernel_gbps": bases / (float(np.mean(ms_a)) * 1e-3) / 1e9,
+        "kernel_ms": kern_ms, "ascii_kernel_ms": ascii_ms,
+        "ascii_kernel_gbps": bases / (ascii_ms * 1e-3) / 1e9,
         "e2e": {"value": bases / float(np.mean(e2e)) / 1e9, "unit": "Gbp/s",
                 "h2d_bytes_per_step": int((b1["h2d_bytes"] - b0["h2d_bytes"]) // runs),
                 "d2h_bytes_per_step": int((b1["d2h_bytes"] - b0["d2h_bytes"]) // runs)},
         "roofline_pcie": pcie,
+        "roofline_ascii": {"bound": "hbm", "achieved": ascii_bytes / (ascii_ms * 1e-3) / 1e9, "peak": hbm_gbs, "unit": "GB/s",
+                           "frac": ascii_bytes / (ascii_ms * 1e-3) / 1e9 / hbm_gbs, "algorithmic_bytes": ascii_bytes,
+                           "what": "tnf_count_ascii2_kernel, the kernel rg_tnf_count_ascii runs (1 B per base)"},
+        "sketch": sketch,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                      "frac": achieved / hbm_gbs, "traffic": None, "algorithmic_bytes": algo_bytes},
         "host_generate_s": gen_s, "host_pack_s": pack_s,
