@@ -40,11 +40,15 @@ def main():
     wh, wo, wnk, _ = oracle.sketch_contigs(seq[: int(offs[k])], offs[: k + 1])
     cpu_s = time.perf_counter() - t0
     ok = bool(np.array_equal(so[: k + 1], wo) and np.array_equal(h[: int(wo[-1])], wh) and np.array_equal(nk[:k], wnk))
+    # and the last records (the last slice of the call)
+    k2 = int(np.searchsorted(offs, bases - int(cpu_mbp * 1e6 / 2)))
+    th, to, tnk, _ = oracle.sketch_contigs(seq[int(offs[k2]):], offs[k2:] - offs[k2])
+    ok_tail = bool(np.array_equal(so[k2:] - so[k2], to) and np.array_equal(h[int(so[k2]):], th) and np.array_equal(nk[k2:], tnk))
     res = {"bases": bases, "contigs": n, "hashes": int(so[-1]), "hashes_per_base": int(so[-1]) / bases, "runs": runs,
            "gbp_per_s_e2e": bases / best / 1e9, "gbp_per_s_device": bases / (min(r["device_ms"] for r in runs) * 1e-3) / 1e9,
            "cpu": {"kind": "port (finch restated, oracle/oracle_minhash.c)", "threads": threads, "sample_bases": int(offs[k]),
                    "seconds": cpu_s, "gbp_per_s": int(offs[k]) / cpu_s / 1e9},
-           "parity_prefix_identical": ok}
+           "parity_prefix_identical": ok, "parity_tail_identical": ok_tail}
     res["speedup_vs_cpu_port"] = res["gbp_per_s_e2e"] / res["cpu"]["gbp_per_s"]
     ctx.close()
     os.makedirs(os.path.dirname(out) or ".", exist_ok=True)

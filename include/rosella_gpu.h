@@ -77,7 +77,9 @@ void *rg_stream(rg_handle *h);
  *   "exact_compact"    1 (default) the exhaustive pass collects the rows that pass its FP32 prefilter and evaluates them
  *                      side by side; 0 = in place (A/B only)
  *   "certify"          1 (default) margin certificate + exhaustive f64 pass for uncertified rows; 0 = off (A/B only)
- *   "kprime_depth", "kprime_tnf"   candidate-list length override (0 = automatic; 48 (TNF only), 64, 128 or 256) */
+ *   "kprime_depth", "kprime_tnf"   candidate-list length override (0 = automatic; 48 (TNF only), 64, 128 or 256)
+ *   "sketch_slice_bytes"  bytes of records rg_sketch_contigs processes per slice (0 = 256 MiB; the upload of the next
+ *                      slice overlaps the hashing of the current one) */
 int32_t rg_set_option(rg_handle *h, const char *key, int64_t value);
 
 /* ------------------------------------------------------------------ TNF counting */

@@ -130,6 +130,7 @@ int32_t rg_set_option(rg_handle *h, const char *key, int64_t value) {
     else if (k == "certify") { if (value < 0 || value > 1) return bad(); h->opt_certify = (int)value; }
     else if (k == "kprime_depth") { if (value != 0 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_depth = (uint32_t)value; }
     else if (k == "kprime_tnf") { if (value != 0 && value != 48 && value != 64 && value != 128 && value != 256) return bad(); h->opt_kprime_tnf = (uint32_t)value; }
+    else if (k == "sketch_slice_bytes") { if (value < 0 || value > (1ll << 31) - 1) return bad(); h->opt_sketch_slice = (uint64_t)value; }
     else return rg_fail(h, RG_ERR_INVALID, "rg_set_option: unknown key \"%s\"", key);
     return RG_OK;
 }

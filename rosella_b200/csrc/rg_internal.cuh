@@ -94,6 +94,7 @@ struct rg_handle {
     int opt_tnf_fp32 = 0;             // 1 = force the FP32 CUDA-core TNF select
     int opt_exact_compact = 1;        // 0 = the exhaustive pass evaluates passing rows in place (A/B only)
     int opt_certify = 1;              // 0 = skip the margin certificate and the exhaustive pass (A/B measurements only)
+    uint64_t opt_sketch_slice = 0;    // bytes of records per slice of rg_sketch_contigs (0 = 256 MiB; test hook)
     uint32_t opt_kprime_depth = 0, opt_kprime_tnf = 0;   // candidate-list override (test hook; 0 = automatic)
 
     // ---- TNF counting state

@@ -8,7 +8,7 @@
 // (first half); the sketch is the distinct hashes <= max_hash = u64::MAX / (1/scale), padded with the next smallest
 // distinct hashes while it has fewer than kmers_to_sketch = (normalised length x scale) entries; ascending.
 //
-// Device pipeline per slice of records (<= 1 GiB of bytes, so every count fits an int for cub):
+// Device pipeline per slice of records (256 MiB of bytes by default, so every count fits an int for cub):
 //   1. hash kernel, COUNT pass: a thread owns 64 raw bytes of one record, rebuilds the rolling k-mer state from the
 //      bytes before them, hashes every k-mer that ENDS in its bytes and counts those with hash <= T (T = 1.5 max_hash);
 //   2. exclusive scan of the per-thread counts = where each thread writes: candidates of a record are contiguous, no
@@ -19,6 +19,7 @@
 //      A record whose candidates do not reach kmers_to_sketch (repeats, long N runs: rare) is flagged and steps 1-5 are
 //      repeated for the flagged records alone with T = u64::MAX, so the result never depends on T;
 //   6. scan of the kept lengths = the sketch offsets; compact kernel writes the kept distinct hashes.
+// The upload of slice i + 1 runs on a copy stream beside steps 1-6 of slice i (two alternating buffers).
 // The hash kernel is integer-ALU bound (about 220 instructions per k-mer: 12 64-bit multiplies of MurmurHash3 and the
 // 2-bit -> ASCII expansion of the canonical k-mer through PRMT), one byte of HBM traffic per k-mer.
 #include <cub/device/device_scan.cuh>
@@ -34,7 +35,7 @@ namespace {
 
 constexpr uint32_t SEG = 64;                 // raw bytes per thread
 constexpr int HT = 128;                      // threads per CTA of the hash kernel
-constexpr uint64_t SLICE_BYTES = 1ull << 30;
+constexpr uint64_t SLICE_BYTES = 256ull << 20;   // default slice; rg_set_option("sketch_slice_bytes") overrides (test hook)
 
 __device__ __forceinline__ uint64_t rotl64(uint64_t x, int r) { return (x << r) | (x >> (64 - r)); }
 __device__ __forceinline__ uint64_t fmix64(uint64_t k) {
@@ -245,7 +246,12 @@ struct SliceCtx {
 };
 
 // steps 1-4 for the work items `ids` (NULL: all m records of the slice) with candidate threshold thr
-int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, uint64_t thr, bool with_counts, uint32_t *total_out, bool *timed) {
+// after_small_copies (may be empty) runs once, right after the pass has queued its small host->device copies: the
+// host->device copy engine is a FIFO across streams, so the large upload of the NEXT slice must be queued behind them —
+// queued before, every slice would wait for the next slice's upload and nothing would overlap (measured).
+template <class F>
+int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, uint64_t thr, bool with_counts, uint32_t *total_out, bool *timed,
+                 F after_small_copies) {
     *timed = false;
     rg_handle *h = c.h;
     int32_t rc = RG_OK;
@@ -263,7 +269,7 @@ int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, u
     SK_TRY(rg_reserve(h, P.begin, ((size_t)m + 1) * sizeof(int)));
     if (n_seg == 0) {
         SK_CUDA(cudaMemsetAsync(P.begin.p, 0, ((size_t)m + 1) * sizeof(int), h->stream));
-        return RG_OK;
+        return after_small_copies();
     }
     SK_TRY(rg_reserve(h, P.seg_start, ((size_t)m + 1) * 4));
     SK_TRY(rg_reserve(h, P.seg_cnt, ((size_t)n_seg + 1) * 4));
@@ -275,6 +281,7 @@ int32_t run_pass(const SliceCtx &c, Pass &P, const std::vector<uint32_t> *ids, u
         SK_CUDA(cudaMemcpyAsync(P.rec_ids.p, ids->data(), (size_t)m * 4, cudaMemcpyHostToDevice, h->stream));
         d_ids = (const uint32_t *)P.rec_ids.p;
     }
+    SK_TRY(after_small_copies());
     SK_CUDA(cudaMemsetAsync((uint32_t *)P.seg_cnt.p + n_seg, 0, 4, h->stream));
     const unsigned grid = (n_seg + HT - 1) / HT;
     cudaEventRecord(h->ev[5], h->stream);
@@ -331,10 +338,28 @@ int32_t grow_preserve(rg_handle *h, DevBuf &b, size_t used, size_t bytes) {
     return RG_OK;
 }
 
+struct Uploader {                 // the copy stream that uploads slice i + 1 while slice i is hashed and sorted
+    cudaStream_t cs = nullptr;
+    cudaEvent_t t0[2] = {}, done[2] = {};
+    int32_t create(rg_handle *h) {
+        cudaError_t e = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
+        for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+            e = cudaEventCreate(&t0[i]);
+            if (e == cudaSuccess) e = cudaEventCreate(&done[i]);
+        }
+        return e == cudaSuccess ? RG_OK : rg_fail(h, RG_ERR_CUDA, "rg_sketch_contigs: copy stream: %s", cudaGetErrorString(e));
+    }
+    void destroy() {
+        if (cs) cudaStreamSynchronize(cs);
+        for (int i = 0; i < 2; ++i) { if (t0[i]) cudaEventDestroy(t0[i]); if (done[i]) cudaEventDestroy(done[i]); }
+        if (cs) cudaStreamDestroy(cs);
+    }
+};
+
 int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, uint64_t n, uint32_t k, double scale, uint64_t seed,
-                    uint64_t *sketch_offsets, uint64_t *n_valid_kmers, Pass &P0, Pass &P1, DevBuf (&B)[12]) {
+                    uint64_t *sketch_offsets, uint64_t *n_valid_kmers, Pass &P0, Pass &P1, DevBuf (&B)[13], Uploader &up) {
     int32_t rc = RG_OK;
-    DevBuf &d_seq = B[0], &d_off = B[1], &d_cls = B[2], &d_nk = B[3], &d_nl = B[4], &d_keep = B[5], &d_sb = B[6], &d_sc = B[7],
+    DevBuf &d_seq0 = B[0], &d_seq1 = B[12], &d_off = B[1], &d_cls = B[2], &d_nk = B[3], &d_nl = B[4], &d_keep = B[5], &d_sb = B[6], &d_sc = B[7],
            &d_sel = B[8], &d_flag = B[9], &d_soff = B[10], &d_tmp = B[11];
     uint8_t cls[256];
     rg::build_class_table(cls);
@@ -347,26 +372,42 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
     SK_TRY(rg_reserve(h, h->skt_hash, (size_t)((double)total_bytes * scale * 1.15) * 8 + (1 << 20)));
     h->skt_total = 0;
     sketch_offsets[0] = 0;
+    const uint64_t slice_bytes = h->opt_sketch_slice ? h->opt_sketch_slice : SLICE_BYTES;
+    std::vector<std::pair<uint64_t, uint64_t>> slices;
     for (uint64_t r0 = 0; r0 < n;) {
         uint64_t r1 = r0 + 1;
-        while (r1 < n && offsets[r1 + 1] - offsets[r0] <= SLICE_BYTES && r1 - r0 < 0x7fffff00ull) ++r1;
+        while (r1 < n && offsets[r1 + 1] - offsets[r0] <= slice_bytes && r1 - r0 < 0x7fffff00ull) ++r1;
+        if (offsets[r1] - offsets[r0] > 0x7fffffffull)
+            return rg_fail(h, RG_ERR_INVALID, "rg_sketch_contigs: record %llu is longer than 2 GiB", (unsigned long long)r0);
+        slices.emplace_back(r0, r1);
+        r0 = r1;
+    }
+    // slice si goes to buffer si & 1 on the copy stream; the buffer's previous user (slice si - 2) is complete
+    auto upload = [&](size_t si) -> int32_t {
+        int32_t rc = RG_OK;
+        const uint64_t sb = offsets[slices[si].first], bytes = offsets[slices[si].second] - sb;
+        DevBuf &dst = (si & 1) ? d_seq1 : d_seq0;
+        SK_TRY(rg_reserve(h, dst, bytes + 16));
+        cudaEventRecord(up.t0[si & 1], up.cs);
+        if (bytes) SK_CUDA(cudaMemcpyAsync(dst.p, seq + sb, bytes, cudaMemcpyHostToDevice, up.cs));
+        cudaEventRecord(up.done[si & 1], up.cs);
+        return RG_OK;
+    };
+    SK_TRY(upload(0));
+    for (size_t si = 0; si < slices.size(); ++si) {
+        const uint64_t r0 = slices[si].first, r1 = slices[si].second;
         const uint32_t m = (uint32_t)(r1 - r0);
         const uint64_t sb = offsets[r0], bytes = offsets[r1] - sb;
-        if (bytes > 0x7fffffffull) return rg_fail(h, RG_ERR_INVALID, "rg_sketch_contigs: record %llu is longer than 2 GiB", (unsigned long long)r0);
         std::vector<uint64_t> off((size_t)m + 1);
         for (uint32_t j = 0; j <= m; ++j) off[j] = offsets[r0 + j] - sb;
-        SK_TRY(rg_reserve(h, d_seq, bytes + 16));
+        DevBuf &d_seq = (si & 1) ? d_seq1 : d_seq0;
         SK_TRY(rg_reserve(h, d_off, ((size_t)m + 1) * 8));
         for (DevBuf *b : {&d_nk, &d_nl, &d_keep, &d_sb}) SK_TRY(rg_reserve(h, *b, ((size_t)m + 1) * 8));
         SK_TRY(rg_reserve(h, d_soff, ((size_t)m + 1) * 8));
         SK_TRY(rg_reserve(h, d_sc, (size_t)m * 4));
         SK_TRY(rg_reserve(h, d_sel, m));
         SK_TRY(rg_reserve(h, d_flag, m));
-        cudaEventRecord(h->ev[5], h->stream);
-        if (bytes) SK_CUDA(cudaMemcpyAsync(d_seq.p, seq + sb, bytes, cudaMemcpyHostToDevice, h->stream));
-        cudaEventRecord(h->ev[6], h->stream);
-        SK_CUDA(cudaEventSynchronize(h->ev[6]));
-        h->tm.h2d_ms += rg_elapsed(h->ev[5], h->ev[6]);
+        SK_CUDA(cudaStreamWaitEvent(h->stream, up.done[si & 1], 0));
         SK_CUDA(cudaMemcpyAsync(d_off.p, off.data(), ((size_t)m + 1) * 8, cudaMemcpyHostToDevice, h->stream));
         SK_CUDA(cudaMemsetAsync(d_nk.p, 0, ((size_t)m + 1) * 8, h->stream));
         SK_CUDA(cudaMemsetAsync(d_nl.p, 0, ((size_t)m + 1) * 8, h->stream));
@@ -378,7 +419,9 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
                    (unsigned long long *)d_nk.p, (unsigned long long *)d_nl.p};
         uint32_t total0 = 0, total1 = 0;
         bool timed0 = false, timed1 = false;
-        SK_TRY(run_pass(c, P0, nullptr, thr, true, &total0, &timed0));
+        // the next slice's upload overlaps everything below; it is queued from inside the pass (see run_pass)
+        SK_TRY(run_pass(c, P0, nullptr, thr, true, &total0, &timed0,
+                        [&]() -> int32_t { return si + 1 < slices.size() ? upload(si + 1) : (int32_t)RG_OK; }));
         const unsigned wgrid = (unsigned)(((uint64_t)m * 32 + 255) / 256);
         sketch_select_kernel<<<wgrid, 256, 0, h->stream>>>((const uint64_t *)P0.sorted.p, (const int *)P0.begin.p, nullptr, m, max_hash, thr, scale,
                                                            (const unsigned long long *)d_nl.p, (const unsigned long long *)d_nk.p,
@@ -396,7 +439,7 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
             std::vector<uint32_t> ids;
             ids.reserve(n_flag);
             for (uint32_t j = 0; j < m; ++j) if (flag[j]) ids.push_back(j);
-            SK_TRY(run_pass(c, P1, &ids, ~0ull, false, &total1, &timed1));
+            SK_TRY(run_pass(c, P1, &ids, ~0ull, false, &total1, &timed1, []() -> int32_t { return RG_OK; }));
             (void)timed1;
             const unsigned fgrid = (unsigned)(((uint64_t)ids.size() * 32 + 255) / 256);
             sketch_select_kernel<<<fgrid, 256, 0, h->stream>>>((const uint64_t *)P1.sorted.p, (const int *)P1.begin.p, (const uint32_t *)P1.rec_ids.p,
@@ -427,7 +470,7 @@ int32_t sketch_impl(rg_handle *h, const uint8_t *seq, const uint64_t *offsets, u
         h->tm.kernel_launches += 2;
         h->tm.d2h_bytes += (size_t)m * 8 * (n_valid_kmers ? 2 : 1);
         h->skt_total = base + slice_total;
-        r0 = r1;
+        h->tm.h2d_ms += rg_elapsed(up.t0[si & 1], up.done[si & 1]);     // complete: h->stream waited for it and was synchronised
     }
     return RG_OK;
 }
@@ -452,12 +495,15 @@ extern "C" int32_t rg_sketch_contigs(rg_handle *h, const uint8_t *seq, const uin
     if (n_hashes) *n_hashes = 0;
     if (n == 0) return RG_OK;
     Pass P0, P1;
-    DevBuf B[12];
+    DevBuf B[13];
+    Uploader up;
+    int32_t rc = up.create(h);
     h->tm.h2d_ms = h->tm.transform_ms = h->tm.rescore_ms = 0.0;
     cudaEventRecord(h->ev[3], h->stream);
-    const int32_t rc = sketch_impl(h, seq, offsets, n, kmer_length, scale, seed, sketch_offsets, n_valid_kmers, P0, P1, B);
+    if (rc == RG_OK) rc = sketch_impl(h, seq, offsets, n, kmer_length, scale, seed, sketch_offsets, n_valid_kmers, P0, P1, B, up);
     cudaEventRecord(h->ev[4], h->stream);
     cudaStreamSynchronize(h->stream);
+    up.destroy();
     if (rc == RG_OK) h->tm.select_ms = rg_elapsed(h->ev[3], h->ev[4]);
     P0.release(); P1.release();
     for (DevBuf &b : B) rg_release(b);

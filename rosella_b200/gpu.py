@@ -88,7 +88,7 @@ class Context:
             raise RosellaGpuError(rc, (self.lib.rg_last_error(self.h) or b"").decode())
 
     def set_option(self, key: str, value: int):
-        """rg_set_option: depth_build, sym_block, sym_chunk, tnf_select_impl, certify, kprime_depth, kprime_tnf."""
+        """rg_set_option: depth_build, sym_block, sym_chunk, tnf_select_impl, certify, kprime_depth, kprime_tnf, sketch_slice_bytes."""
         self._chk(self.lib.rg_set_option(self.h, key.encode(), int(value)))
 
     def sync(self):

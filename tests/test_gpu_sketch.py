@@ -33,6 +33,25 @@ def test_synthetic_contigs_and_wrapped_fasta(ctx):
     assert np.array_equal(hw, h[: int(o[20])])                 # line breaks are removed by normalize(false)
 
 
+def test_many_slices_and_records_longer_than_a_slice(ctx):
+    """rg_sketch_contigs works through slices of records (256 MiB by default) with the upload of the next slice running
+    beside the hashing of the current one on a copy stream, two alternating device buffers.  With 100 kB slices the
+    3 Mbp set takes about 40 of them, several records are longer than a slice (a slice of their own), and the result
+    must not change."""
+    seq, offs = synth.contigs(3_000_000, threads=4, seed=12)
+    assert (np.diff(offs.astype(np.int64)) > 100_000).sum() >= 3
+    want = ctx.sketch_contigs(seq, offs)
+    try:
+        for slice_bytes in (100_000, 37_777, 1_000_000):
+            ctx.set_option("sketch_slice_bytes", slice_bytes)
+            for a, b in zip(ctx.sketch_contigs(seq, offs), want):
+                assert np.array_equal(a, b), slice_bytes
+    finally:
+        ctx.set_option("sketch_slice_bytes", 0)
+    wh, wo, wnk, _ = oracle.sketch_contigs(seq, offs)
+    assert np.array_equal(want[0], wh) and np.array_equal(want[1], wo) and np.array_equal(want[2], wnk)
+
+
 def test_edge_cases_and_the_redo_path(ctx):
     rng = np.random.default_rng(31)
     alpha = np.frombuffer(b"ACGT", np.uint8)
