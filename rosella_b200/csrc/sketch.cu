@@ -20,7 +20,7 @@
 //      repeated for the flagged records alone with T = u64::MAX, so the result never depends on T;
 //   6. scan of the kept lengths = the sketch offsets; compact kernel writes the kept distinct hashes.
 // The upload of slice i + 1 runs on a copy stream beside steps 1-6 of slice i (two alternating buffers).
-// The hash kernel is integer-ALU bound (about 220 instructions per k-mer: 12 64-bit multiplies of MurmurHash3 and the
+// The hash kernel is integer-ALU bound (309 warp instructions per 32 k-mers and the ALU pipe at 82-84 % under ncu, profiles/r2y_*: 12 64-bit multiplies of MurmurHash3 and the
 // 2-bit -> ASCII expansion of the canonical k-mer through PRMT), one byte of HBM traffic per k-mer.
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_segmented_sort.cuh>
