@@ -45,6 +45,8 @@ def load() -> C.CDLL:
         "rh_fastx_offsets": (C.POINTER(C.c_uint64), [vp]),
         "rh_count_kmers": (vp, [C.c_int, C.c_char_p, C.c_char_p, C.c_int]),
         "rh_sketch_contigs": (vp, [C.c_int, C.c_char_p, sz, sz, C.c_double, C.c_uint64]),
+        "rh_sketches_new": (vp, [C.POINTER(C.c_char_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), sz]),
+        "rh_sketches_filter_by_index": (C.c_int, [vp, C.POINTER(sz), sz]),
         "rh_sketches_free": (None, [vp]), "rh_sketches_n": (sz, [vp]), "rh_sketches_name": (C.c_char_p, [vp, sz]),
         "rh_sketches_offsets": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_hashes": (C.POINTER(C.c_uint64), [vp]),
         "rh_sketches_num_valid_kmers": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_seq_length": (C.POINTER(C.c_uint64), [vp]),
@@ -169,6 +171,36 @@ def count_kmers(assembly: str, output_directory: str, no_flight: bool = False, d
     return KmerFrequencyTable(load().rh_count_kmers(device, assembly.encode(), output_directory.encode(), int(no_flight)))
 
 
+def _sketches_out(lib, h):
+    n = lib.rh_sketches_n(h)
+    names = [lib.rh_sketches_name(h, i).decode() for i in range(n)]
+    offs = np.ctypeslib.as_array(lib.rh_sketches_offsets(h), (n + 1,)).copy()
+    total = int(offs[-1])
+    hashes = np.ctypeslib.as_array(lib.rh_sketches_hashes(h), (total,)).copy() if total else np.zeros(0, np.uint64)
+    nk = np.ctypeslib.as_array(lib.rh_sketches_num_valid_kmers(h), (n,)).copy() if n else np.zeros(0, np.uint64)
+    sl = np.ctypeslib.as_array(lib.rh_sketches_seq_length(h), (n,)).copy() if n else np.zeros(0, np.uint64)
+    return names, hashes, offs, nk, sl
+
+
+def sketch_result_filter_by_index(names, hashes, offsets, indices_to_remove):
+    """ContigSketchResult::filter_by_index (contig_sketcher.rs:158-176) on caller data -> (names, hashes, offsets)"""
+    lib = load()
+    arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    hashes = np.ascontiguousarray(hashes, np.uint64) if len(hashes) else np.zeros(1, np.uint64)
+    h = lib.rh_sketches_new(arr, offsets.ctypes.data_as(C.POINTER(C.c_uint64)), hashes.ctypes.data_as(C.POINTER(C.c_uint64)), len(names))
+    if not h:
+        raise _err()
+    try:
+        idx = (C.c_size_t * len(indices_to_remove))(*sorted(indices_to_remove))
+        if lib.rh_sketches_filter_by_index(h, idx, len(indices_to_remove)):
+            raise _err()
+        out = _sketches_out(lib, h)
+    finally:
+        lib.rh_sketches_free(h)
+    return out[0], out[1], out[2]
+
+
 def sketch_contigs(assembly: str, min_contig_size: int = 1500, kmer_size: int = 31, sketch_scale: float = 0.1, seed: int = 42,
                    device: int = 0):
     """sketch_contigs(m) (contig_sketcher.rs:11-92) on the GPU
@@ -178,16 +210,9 @@ def sketch_contigs(assembly: str, min_contig_size: int = 1500, kmer_size: int = 
     if not h:
         raise _err()
     try:
-        n = lib.rh_sketches_n(h)
-        names = [lib.rh_sketches_name(h, i).decode() for i in range(n)]
-        offs = np.ctypeslib.as_array(lib.rh_sketches_offsets(h), (n + 1,)).copy()
-        total = int(offs[-1])
-        hashes = np.ctypeslib.as_array(lib.rh_sketches_hashes(h), (total,)).copy() if total else np.zeros(0, np.uint64)
-        nk = np.ctypeslib.as_array(lib.rh_sketches_num_valid_kmers(h), (n,)).copy() if n else np.zeros(0, np.uint64)
-        sl = np.ctypeslib.as_array(lib.rh_sketches_seq_length(h), (n,)).copy() if n else np.zeros(0, np.uint64)
+        return _sketches_out(lib, h)
     finally:
         lib.rh_sketches_free(h)
-    return names, hashes, offs, nk, sl
 
 
 class KGraphResult:

@@ -110,6 +110,7 @@ struct rh_sketches {
     ContigSketchResult r;
     std::vector<uint64_t> offsets, hashes, num_valid_kmers, seq_length;
 };
+static void rh_sketches_flatten(rh_sketches *p);
 rh_sketches *rh_sketch_contigs(int device, const char *assembly, size_t min_contig_size, size_t kmer_size, double scale, uint64_t seed) {
     rh_sketches *out = nullptr;
     if (guard([&] {
@@ -117,16 +118,43 @@ rh_sketches *rh_sketch_contigs(int device, const char *assembly, size_t min_cont
             SketchContigsArgs m{assembly, min_contig_size, SketchSettings{kmer_size, scale, seed}};
             auto p = std::make_unique<rh_sketches>();
             p->r = sketch_contigs(gpu, m);
-            p->offsets.push_back(0);
-            for (const Sketch &s : p->r.contig_sketches) {
-                p->hashes.insert(p->hashes.end(), s.hashes.begin(), s.hashes.end());
-                p->offsets.push_back(p->hashes.size());
-                p->num_valid_kmers.push_back(s.num_valid_kmers);
-                p->seq_length.push_back(s.seq_length);
-            }
+            rh_sketches_flatten(p.get());
             out = p.release();
         })) return nullptr;
     return out;
+}
+// a ContigSketchResult from caller data (tests of filter_by_index need no GPU)
+rh_sketches *rh_sketches_new(const char *const *names, const uint64_t *offsets, const uint64_t *hashes, size_t n) {
+    rh_sketches *out = nullptr;
+    if (guard([&] {
+            auto p = std::make_unique<rh_sketches>();
+            for (size_t i = 0; i < n; ++i) {
+                Sketch sk;
+                sk.name = names[i];
+                sk.hashes.assign(hashes + offsets[i], hashes + offsets[i + 1]);
+                p->r.contig_names.emplace_back(names[i]);
+                p->r.contig_sketches.push_back(std::move(sk));
+            }
+            rh_sketches_flatten(p.get());
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
+static void rh_sketches_flatten(rh_sketches *p) {
+    p->offsets.assign(1, 0); p->hashes.clear(); p->num_valid_kmers.clear(); p->seq_length.clear();
+    for (const Sketch &s : p->r.contig_sketches) {
+        p->hashes.insert(p->hashes.end(), s.hashes.begin(), s.hashes.end());
+        p->offsets.push_back(p->hashes.size());
+        p->num_valid_kmers.push_back(s.num_valid_kmers);
+        p->seq_length.push_back(s.seq_length);
+    }
+}
+int rh_sketches_filter_by_index(rh_sketches *s, const size_t *idx, size_t n) {
+    return guard([&] {
+        s->r.filter_by_index(std::set<size_t>(idx, idx + n));
+        if (s->r.contig_names.size() != s->r.contig_sketches.size()) throw Error("ContigSketchResult: names and sketches differ in length");
+        rh_sketches_flatten(s);
+    });
 }
 void rh_sketches_free(rh_sketches *s) { delete s; }
 size_t rh_sketches_n(const rh_sketches *s) { return s->r.contig_names.size(); }

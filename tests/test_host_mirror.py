@@ -135,6 +135,19 @@ def test_clr_and_k_clamp():
     assert host.clamp_n_neighbours(300, 30) == 30 and host.clamp_n_neighbours(10, 30) == 5
 
 
+def test_contig_sketch_result_filter_by_index():
+    """ContigSketchResult::filter_by_index (contig_sketcher.rs:158-176): names and sketches lose the same positions."""
+    names = [f"c{i}" for i in range(6)]
+    lists = [np.arange(i * 10, i * 10 + i, dtype=np.uint64) for i in range(6)]           # lengths 0..5
+    offs = np.zeros(7, np.uint64); offs[1:] = np.cumsum([len(x) for x in lists])
+    hashes = np.concatenate(lists)
+    got_n, got_h, got_o = host.sketch_result_filter_by_index(names, hashes, offs, {0, 3, 5, 17})
+    assert got_n == ["c1", "c2", "c4"]
+    assert list(got_o) == [0, 1, 3, 7] and np.array_equal(got_h, np.concatenate([lists[1], lists[2], lists[4]]))
+    got_n, got_h, got_o = host.sketch_result_filter_by_index(names, hashes, offs, set())
+    assert got_n == names and np.array_equal(got_o, offs) and np.array_equal(got_h, hashes)
+
+
 def _write_fasta(path, ids, seqs, width=60, gz=False):
     text = "".join(f">{i}\n" + "".join(s[p:p + width] + "\n" for p in range(0, len(s), width)) for i, s in zip(ids, seqs))
     if gz:
