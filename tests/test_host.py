@@ -123,3 +123,42 @@ def test_reference_arm_ignores_omp_num_threads_and_mirrors_the_gpu_config():
         n, samples, k, gpus, query_rows = 40000, 3, 10, 4, 0
     assert d["config"] == bench.workload_config(A, min(bench.DEFAULT_QUERY_ROWS, A.n // 4), 4)
     assert "reference_code" in d["cpu_baseline"]
+
+
+def test_register_classifier_model_of_the_ascii_tnf_kernel():
+    """tnf_count2.cu classify4 in integer arithmetic: `byte & 7` keys two PRMT tables; (byte ^ expected) & 0xDF == 0 must
+    hold exactly for the ten bytes needletail's normalize(false) turns into A/C/G/T, and the packing multiply must put the
+    four 2-bit codes in order.  A model of the device code (same constants), checked for every byte value at every
+    position; the kernel itself is compared with the oracle on the GPU (tests/test_gpu_tnf.py)."""
+    import random
+
+    def byte_perm(x, y, s):
+        src = [(x >> (8 * i)) & 0xFF for i in range(4)] + [(y >> (8 * i)) & 0xFF for i in range(4)]
+        return sum(src[(s >> (4 * i)) & 0x7] << (8 * i) for i in range(4))
+
+    def classify4(w):
+        v = w & 0x07070707
+        t = (v * 0x1001) & 0xFFFFFFFF
+        sel = byte_perm(t, 0, 0x0031)
+        exp = byte_perm(0x43FF41FF, 0x47FF5554, sel)
+        cod = byte_perm(0x01000000, 0x02000303, sel)
+        bad = byte_perm(w, 0, 0x2301) ^ exp
+        return ((cod * 0x04014010) & 0xFFFFFFFF) >> 24, bad
+
+    code = {ord(c): v for c, v in zip("ACGTUacgtu", [0, 1, 2, 3, 3, 0, 1, 2, 3, 3])}
+    rnd = random.Random(1)
+    bases = list(code)
+    for pos in range(4):
+        for b in range(256):
+            for _ in range(8):
+                bs = [rnd.choice(bases) for _ in range(4)]
+                bs[pos] = b
+                w = sum(x << (8 * i) for i, x in enumerate(bs))
+                packed, bad = classify4(w)
+                ok = (bad & 0xDFDFDFDF) == 0
+                assert ok == all(x in code for x in bs), (bs, hex(bad))
+                if ok:
+                    assert packed == sum(code[x] << (2 * i) for i, x in enumerate(bs))
+    for _ in range(50000):
+        w = rnd.getrandbits(32)
+        assert ((classify4(w)[1] & 0xDFDFDFDF) == 0) == all(((w >> (8 * i)) & 0xFF) in code for i in range(4))
