@@ -309,3 +309,66 @@ def test_sketch_contigs_restatement_properties():
     assert len(sk[6]) == 2 and nk[6] == 8000 - 30
     # one k-mer: kept whatever its hash (1 <= kmers_to_sketch = 3)
     assert len(sk[3]) == 1 and len(sk[4]) == 0
+
+
+def test_device_kmer_hash_model_for_every_k():
+    """sketch.cu murmur_kmer in integer arithmetic (same constants and bit tricks: 2-bit canonical k-mer -> four ASCII
+    words through the nibble-spread + PRMT look-up, bytes past k zeroed, the zero-padded tail words) against
+    MurmurHash3_x64_128 of the k-mer's ASCII bytes, for every k in 1..32.  The kernel itself is compared with the oracle
+    on the GPU (tests/test_gpu_sketch.py) for seven of these k."""
+    M = (1 << 64) - 1
+
+    def byte_perm(x, y, s):
+        src = [(x >> (8 * i)) & 0xFF for i in range(4)] + [(y >> (8 * i)) & 0xFF for i in range(4)]
+        return sum(src[(s >> (4 * i)) & 0x7] << (8 * i) for i in range(4))
+
+    def four(y):
+        t = (y | (y << 4)) & 0x0F0F
+        t = (t | (t << 2)) & 0x3333
+        return byte_perm(byte_perm(0x54474341, 0, t), 0, 0x0123)
+
+    def ascii8(x16):
+        return four((x16 >> 8) & 0xFF) | (four(x16 & 0xFF) << 32)
+
+    rotl = lambda x, r: ((x << r) | (x >> (64 - r))) & M
+
+    def fmix(k):
+        k ^= k >> 33; k = k * 0xff51afd7ed558ccd & M; k ^= k >> 33; k = k * 0xc4ceb9fe1a85ec53 & M; k ^= k >> 33
+        return k
+
+    def murmur_kmer(canon, k, seed):
+        c1, c2 = 0x87c37b91114253d5, 0x4cf5ad432745937f
+        x = (canon << (64 - 2 * k)) & M
+        w = [ascii8((x >> 48) & 0xFFFF), ascii8((x >> 32) & 0xFFFF), ascii8((x >> 16) & 0xFFFF), ascii8(x & 0xFFFF)]
+        for i in range(4):
+            have = k - 8 * i
+            w[i] = w[i] if have >= 8 else (0 if have <= 0 else w[i] & ((1 << (8 * have)) - 1))
+        h = [seed, seed]
+
+        def block(k1, k2):
+            k1 = k1 * c1 & M; k1 = rotl(k1, 31); k1 = k1 * c2 & M; h[0] ^= k1
+            h[0] = rotl(h[0], 27); h[0] = (h[0] + h[1]) & M; h[0] = (h[0] * 5 + 0x52dce729) & M
+            k2 = k2 * c2 & M; k2 = rotl(k2, 33); k2 = k2 * c1 & M; h[1] ^= k2
+            h[1] = rotl(h[1], 31); h[1] = (h[1] + h[0]) & M; h[1] = (h[1] * 5 + 0x38495ab5) & M
+
+        if k >= 32:
+            block(w[0], w[1]); block(w[2], w[3]); t1 = t2 = 0
+        elif k >= 16:
+            block(w[0], w[1]); t1, t2 = w[2], w[3]
+        else:
+            t1, t2 = w[0], w[1]
+        t2 = t2 * c2 & M; t2 = rotl(t2, 33); t2 = t2 * c1 & M; h[1] ^= t2
+        t1 = t1 * c1 & M; t1 = rotl(t1, 31); t1 = t1 * c2 & M; h[0] ^= t1
+        h1, h2 = h[0] ^ k, h[1] ^ k
+        h1 = (h1 + h2) & M; h2 = (h2 + h1) & M
+        return (fmix(h1) + fmix(h2)) & M
+
+    rng = np.random.default_rng(3)
+    for k in range(1, 33):
+        for seed in (42, 0, 0xdeadbeefcafe):
+            codes = rng.integers(0, 4, k)
+            canon = 0
+            for c in codes:
+                canon = (canon << 2) | int(c)
+            kmer = bytes(b"ACGT"[int(c)] for c in codes)
+            assert murmur_kmer(canon, k, seed) == oracle.murmur3_x64_128(kmer, seed)[0], (k, seed)
