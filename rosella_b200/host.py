@@ -50,6 +50,15 @@ def load() -> C.CDLL:
         "rh_sketches_free": (None, [vp]), "rh_sketches_n": (sz, [vp]), "rh_sketches_name": (C.c_char_p, [vp, sz]),
         "rh_sketches_offsets": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_hashes": (C.POINTER(C.c_uint64), [vp]),
         "rh_sketches_num_valid_kmers": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_seq_length": (C.POINTER(C.c_uint64), [vp]),
+        "rh_recover_new": (vp, [dp, sz, sz, dp, sz, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), sz, C.c_int,
+                                C.c_uint32, C.c_double]),
+        "rh_recover_free": (None, [vp]), "rh_recover_n_contigs": (sz, [vp]), "rh_recover_prefilter_rounds": (sz, [vp]),
+        "rh_recover_n_filtered": (sz, [vp]), "rh_recover_is_filtered": (C.c_int, [vp, C.c_char_p]),
+        "rh_recover_name": (C.c_char_p, [vp, sz]), "rh_recover_tnf_name": (C.c_char_p, [vp, sz]),
+        "rh_recover_cov_row": (dp, [vp, sz]), "rh_recover_tnf_row": (dp, [vp, sz]), "rh_recover_sketch_len": (C.c_long, [vp, sz]),
+        "rh_recover_retrieve": (C.c_long, [vp, C.POINTER(sz), sz, dp, dp, C.POINTER(C.c_long)]),
+        "rh_recover_filter_contigs": (C.c_int, [vp, C.POINTER(sz), sz]),
+        "rh_recover_prefilter_nodes": (vp, [C.c_int, vp, sz]),
         "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_double]),
         "rh_graph_free": (None, [vp]), "rh_graph_nb_nodes": (sz, [vp]), "rh_graph_max_nbng": (sz, [vp]),
@@ -254,6 +263,81 @@ class KGraphResult:
         if getattr(self, "_h", None) and _lib is not None:
             _lib.rh_graph_free(self._h)
             self._h = None
+
+
+class RecoverEngine:
+    """The graph driver of RecoverEngine (recover_engine.rs:407-543): tables + prefilter_nodes / filter_contigs /
+    retrieve_contig_data; sketches = (hashes u64, offsets u64[n + 1]) or None."""
+
+    def __init__(self, cov, tnf, names, n_neighbours: int = 100, apply_filters: bool = False, variant: int = 0, sketches=None,
+                 sketch_scale: float = 0.1):
+        c = np.ascontiguousarray(cov, np.float64)
+        t = np.ascontiguousarray(tnf, np.float64)
+        dp, up = C.POINTER(C.c_double), C.POINTER(C.c_uint64)
+        arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+        so = sh = None
+        if sketches is not None:
+            sh_a = np.ascontiguousarray(sketches[0], np.uint64) if len(sketches[0]) else np.zeros(1, np.uint64)
+            so_a = np.ascontiguousarray(sketches[1], np.uint64)
+            sh, so = sh_a.ctypes.data_as(up), so_a.ctypes.data_as(up)
+        self._c, self._d = c.shape[1], t.shape[1]
+        self._h = load().rh_recover_new(c.ctypes.data_as(dp), c.shape[0], c.shape[1], t.ctypes.data_as(dp), t.shape[1], arr, so, sh,
+                                        n_neighbours, int(apply_filters), variant, sketch_scale)
+        if not self._h:
+            raise _err()
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            load().rh_recover_free(self._h)
+            self._h = None
+
+    @property
+    def n_contigs(self) -> int:
+        return load().rh_recover_n_contigs(self._h)
+
+    @property
+    def prefilter_rounds(self) -> int:
+        return load().rh_recover_prefilter_rounds(self._h)
+
+    @property
+    def n_filtered(self) -> int:
+        return load().rh_recover_n_filtered(self._h)
+
+    def is_filtered(self, name: str) -> bool:
+        return bool(load().rh_recover_is_filtered(self._h, name.encode()))
+
+    def names(self):
+        lib = load()
+        out = [lib.rh_recover_name(self._h, i).decode() for i in range(self.n_contigs)]
+        assert out == [lib.rh_recover_tnf_name(self._h, i).decode() for i in range(self.n_contigs)]
+        return out
+
+    def tables(self):
+        """-> (cov [n, c], tnf [n, d], sketch lengths or None) as the engine holds them now"""
+        lib, n = load(), self.n_contigs
+        cov = np.array([np.ctypeslib.as_array(lib.rh_recover_cov_row(self._h, i), (self._c,)).copy() for i in range(n)]).reshape(n, self._c)
+        tnf = np.array([np.ctypeslib.as_array(lib.rh_recover_tnf_row(self._h, i), (self._d,)).copy() for i in range(n)]).reshape(n, self._d)
+        sl = [lib.rh_recover_sketch_len(self._h, i) for i in range(n)]
+        return cov, tnf, (None if n and sl[0] < 0 else sl)
+
+    def retrieve_contig_data(self, indices):
+        idx = sorted(set(int(i) for i in indices))
+        arr = (C.c_size_t * len(idx))(*idx)
+        cov0, tnf0 = np.zeros(len(idx)), np.zeros(len(idx))
+        sl = (C.c_long * max(len(idx), 1))()
+        cnt = load().rh_recover_retrieve(self._h, arr, len(idx), cov0.ctypes.data_as(C.POINTER(C.c_double)),
+                                         tnf0.ctypes.data_as(C.POINTER(C.c_double)), sl)
+        if cnt < 0:
+            raise _err()
+        return cov0[:cnt], tnf0[:cnt], list(sl)[:cnt]
+
+    def filter_contigs(self, nodes):
+        arr = (C.c_size_t * len(nodes))(*[int(i) for i in nodes])
+        if load().rh_recover_filter_contigs(self._h, arr, len(nodes)):
+            raise _err()
+
+    def prefilter_nodes(self, rounds: int = 1, device: int = 0) -> "KGraphResult":
+        return KGraphResult(load().rh_recover_prefilter_nodes(device, self._h, rounds))
 
 
 def build_mutual_kgraph(tnf: np.ndarray, cov: np.ndarray, keep_n_edges: int, n_neighbours: int, max_layers: int = 16,

@@ -164,6 +164,89 @@ const uint64_t *rh_sketches_hashes(const rh_sketches *s) { return s->hashes.data
 const uint64_t *rh_sketches_num_valid_kmers(const rh_sketches *s) { return s->num_valid_kmers.data(); }
 const uint64_t *rh_sketches_seq_length(const rh_sketches *s) { return s->seq_length.data(); }
 
+// ---------------------------------------------------------------- RecoverEngine's graph driver
+RecoverEngine *rh_recover_new(const double *cov, size_t n, size_t c, const double *tnf, size_t d, const char *const *names,
+                              const uint64_t *sketch_offsets, const uint64_t *sketch_hashes, size_t n_neighbours, int apply_filters,
+                              uint32_t variant, double sketch_scale) {
+    RecoverEngine *out = nullptr;
+    if (guard([&] {
+            CoverageTable ct;
+            ct.nrows = n; ct.ncols = c;
+            ct.table.assign(cov, cov + n * c);
+            KmerFrequencyTable kt;
+            kt.nrows = n; kt.ncols = d;
+            kt.kmer_table.assign(tnf, tnf + n * d);
+            ContigSketchResult sk;
+            for (size_t i = 0; i < n; ++i) {
+                ct.contig_names.emplace_back(names[i]);
+                kt.contig_names.emplace_back(names[i]);
+                ct.contig_lengths.push_back(0);
+                double m = 0.0;
+                for (size_t j = 0; j < c; j += 2) m += cov[i * c + j];
+                ct.average_depths.push_back(c ? m / (double)(c / 2) : 0.0);
+                if (sketch_offsets) {
+                    Sketch one;
+                    one.name = names[i];
+                    if (sketch_hashes) one.hashes.assign(sketch_hashes + sketch_offsets[i], sketch_hashes + sketch_offsets[i + 1]);
+                    sk.contig_names.emplace_back(names[i]);
+                    sk.contig_sketches.push_back(std::move(one));
+                }
+            }
+            auto p = std::make_unique<RecoverEngine>(std::move(ct), std::move(kt), std::move(sk));
+            p->n_neighbours = n_neighbours;
+            p->apply_filters = apply_filters != 0;
+            p->variant = variant;
+            p->sketch_scale = sketch_scale;
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
+void rh_recover_free(RecoverEngine *r) { delete r; }
+size_t rh_recover_n_contigs(const RecoverEngine *r) { return r->n_contigs; }
+size_t rh_recover_prefilter_rounds(const RecoverEngine *r) { return r->prefilter_rounds; }
+size_t rh_recover_n_filtered(const RecoverEngine *r) { return r->filtered_contigs.size(); }
+int rh_recover_is_filtered(const RecoverEngine *r, const char *name) { return r->filtered_contigs.count(name) ? 1 : 0; }
+const char *rh_recover_name(const RecoverEngine *r, size_t i) { return r->coverage_table.contig_names.at(i).c_str(); }
+const char *rh_recover_tnf_name(const RecoverEngine *r, size_t i) { return r->tnf_table.contig_names.at(i).c_str(); }
+const double *rh_recover_cov_row(const RecoverEngine *r, size_t i) { return r->coverage_table.row(i); }
+const double *rh_recover_tnf_row(const RecoverEngine *r, size_t i) { return r->tnf_table.row(i); }
+long rh_recover_sketch_len(const RecoverEngine *r, size_t i) {
+    return r->contig_sketches.contig_sketches.empty() ? -1 : (long)r->contig_sketches.contig_sketches.at(i).hashes.size();
+}
+// retrieve_contig_data(indices): per included row its first coverage / TNF value and sketch length, in order; returns the count
+long rh_recover_retrieve(const RecoverEngine *r, const size_t *idx, size_t n, double *cov0, double *tnf0, long *sketch_len) {
+    long cnt = -1;
+    if (guard([&] {
+            const auto data = r->retrieve_contig_data(std::set<size_t>(idx, idx + n));
+            for (size_t i = 0; i < data.size(); ++i) {
+                const ContigInformation &ci = data[i].at(0);
+                cov0[i] = ci.coverage[0]; tnf0[i] = ci.tnf[0];
+                sketch_len[i] = ci.sketch ? (long)ci.sketch_len : -1;
+            }
+            cnt = (long)data.size();
+        })) return -1;
+    return cnt;
+}
+// filter_contigs with a graph whose node i has data id i (what build_mutual_kgraph over all rows returns)
+int rh_recover_filter_contigs(RecoverEngine *r, const size_t *nodes, size_t n) {
+    return guard([&] {
+        std::vector<size_t> ids(r->n_contigs);
+        for (size_t i = 0; i < ids.size(); ++i) ids[i] = i;
+        KGraph g(std::vector<std::vector<OutEdge>>(r->n_contigs), std::move(ids), 0);
+        r->filter_contigs(g, std::vector<size_t>(nodes, nodes + n));
+    });
+}
+rh_graph *rh_recover_prefilter_nodes(int device, RecoverEngine *r, size_t rounds) {
+    rh_graph *out = nullptr;
+    if (guard([&] {
+            Gpu gpu(device);
+            auto p = std::make_unique<rh_graph>();
+            p->g = r->prefilter_nodes(gpu, rounds);
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
+
 // sketch_hashes / sketch_offsets (n + 1 entries) may be NULL: no sketches
 rh_graph *rh_build_mutual_kgraph(int device, const double *tnf, size_t d, const double *cov, size_t c, size_t n,
                                  size_t keep_n_edges, size_t n_neighbours, size_t max_layers, size_t ef_construction,

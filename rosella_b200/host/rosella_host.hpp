@@ -8,7 +8,8 @@
 //   sketch_contigs, ContigSketchResult  src/sketch/contig_sketcher.rs:11-92, :152-176
 //   KGraph / OutEdge                    annembed::fromhnsw::kgraph (third party; the subset the path uses)
 //   mutual_knn / intersect              src/graphs/nearest_neighbour_graph.rs:12-72
-//   RecoverEngine::build_mutual_kgraph  src/recover/recover_engine.rs:510-519 (k clamp)
+//   RecoverEngine graph driver          src/recover/recover_engine.rs:464-543 (prefilter_nodes, filter_contigs,
+//                                       build_mutual_kgraph with the k clamp, retrieve_contig_data); CoverageTable subset
 //
 // Errors: the reference returns anyhow::Result; here every failure throws rosella::Error (the C wrapper
 // in capi.cpp turns it into a status + message).  There is no CPU fallback: a Gpu is required.
@@ -158,6 +159,42 @@ class EmbedderEngine {        // embedder.rs:15-87
     double sketch_scale = 0.1;          // SketchParams::Scaled.scale of the sketches (contig_sketcher.rs:66-71; cli default 0.1)
     // the TNF graph of the last build (the reference builds it as tnf_kgraph, :65)
     mutable KGraph last_tnf_kgraph;
+};
+
+// ------------------------------------------------------------------ RecoverEngine's graph driver (recover_engine.rs:407-543)
+struct CoverageTable {            // src/coverage/coverage_table.rs:9-17, the members the path touches
+    size_t nrows = 0, ncols = 0;                 // ncols = 2 x samples: mean, variance interleaved
+    std::vector<double> table;                   // row-major
+    std::vector<double> average_depths;
+    std::vector<std::string> contig_names;
+    std::vector<size_t> contig_lengths;
+    const double *row(size_t i) const { return table.data() + i * ncols; }
+    std::set<std::string> filter_by_index(const std::set<size_t> &indices_to_remove);   // :69-131, returns the removed names
+};
+
+class RecoverEngine {             // `no_flight` members of recover_engine.rs:48-75 that the graph driver uses
+   public:
+    RecoverEngine(CoverageTable coverage, KmerFrequencyTable tnf, ContigSketchResult sketches);
+    // :522-543
+    std::vector<std::vector<ContigInformation>> retrieve_contig_data(const std::set<size_t> &indices_to_include) const;
+    // :510-519 (k clamp :513-517); node i of the graph = the i-th included row
+    std::pair<KGraph, std::vector<size_t>> build_mutual_kgraph(Gpu &gpu, size_t keep_n_edges,
+                                                               const std::set<size_t> &indices_to_include) const;
+    KGraph prefilter_nodes(Gpu &gpu, size_t rounds);                                      // :464-482
+    void filter_contigs(const KGraph &kgraph, const std::vector<size_t> &disconnected_nodes);   // :485-505
+
+    CoverageTable coverage_table;
+    KmerFrequencyTable tnf_table;
+    ContigSketchResult contig_sketches;          // empty = no sketches (DepthDistance factor 1)
+    size_t n_contigs = 0;
+    size_t n_neighbours = 100, max_layers = 16, ef_construction = 100;   // cli.rs:841-866
+    std::set<std::string> filtered_contigs;
+    double sketch_scale = 0.1;
+    uint32_t variant = RG_VARIANT_RUST;
+    // false = the reference as it stands (intersect / mutual_knn results dropped, so an exact graph with n > k never has a
+    // disconnected node and prefilter_nodes ends after one build); true = the filters its doc comments describe
+    bool apply_filters = false;
+    size_t prefilter_rounds = 0;                 // builds the last prefilter_nodes needed
 };
 
 // nearest_neighbour_graph.rs:12-35 / :38-72.  apply = false reproduces the reference (result dropped).

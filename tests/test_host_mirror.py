@@ -148,6 +148,32 @@ def test_contig_sketch_result_filter_by_index():
     assert got_n == names and np.array_equal(got_o, offs) and np.array_equal(got_h, hashes)
 
 
+def test_recover_engine_tables_follow_filter_contigs():
+    """RecoverEngine::retrieve_contig_data (recover_engine.rs:522-543) hands the included rows in row order; filter_contigs
+    (:485-505) removes the same rows from the coverage table (coverage_table.rs:69-131), the TNF table and the sketches
+    and collects the removed names."""
+    n, s = 12, 2
+    rng = np.random.default_rng(4)
+    cov = rng.random((n, 2 * s)) + np.arange(n)[:, None]              # row i starts with i.xxx
+    tnf = rng.random((n, 136)) + 100 * np.arange(n)[:, None]
+    names = [f"contig_{i}" for i in range(n)]
+    lists = [np.arange(i, dtype=np.uint64) + 1000 * i for i in range(n)]   # sketch of row i has i hashes
+    offs = np.zeros(n + 1, np.uint64); offs[1:] = np.cumsum([len(x) for x in lists])
+    eng = host.RecoverEngine(cov, tnf, names, n_neighbours=3, sketches=(np.concatenate(lists), offs))
+    c0, t0, sl = eng.retrieve_contig_data({7, 2, 9, 2})
+    assert list(c0) == [cov[2, 0], cov[7, 0], cov[9, 0]] and list(t0) == [tnf[2, 0], tnf[7, 0], tnf[9, 0]] and sl == [2, 7, 9]
+    eng.filter_contigs([3, 0, 11])
+    keep = [i for i in range(n) if i not in (0, 3, 11)]
+    assert eng.n_contigs == 9 and eng.names() == [names[i] for i in keep] and eng.n_filtered == 3
+    assert all(eng.is_filtered(names[i]) for i in (0, 3, 11)) and not eng.is_filtered(names[1])
+    c, t, sl = eng.tables()
+    assert np.array_equal(c, cov[keep]) and np.array_equal(t, tnf[keep]) and sl == keep
+    eng.filter_contigs([8])                                           # positions are those of the filtered tables
+    assert eng.names()[-1] == names[9] and eng.n_contigs == 8 and eng.is_filtered(names[10])
+    plain = host.RecoverEngine(cov, tnf, names)                       # no sketches at all
+    assert plain.retrieve_contig_data({1})[2] == [-1] and plain.tables()[2] is None
+
+
 def _write_fasta(path, ids, seqs, width=60, gz=False):
     text = "".join(f">{i}\n" + "".join(s[p:p + width] + "\n" for p in range(0, len(s), width)) for i, s in zip(ids, seqs))
     if gz:
@@ -253,6 +279,49 @@ def test_build_mutual_kgraph_matches_the_exhaustive_oracle():
     for i in range(n):
         assert f.neighbours(i)[0].tolist() == step2[i]
     assert f.disconnected_nodes == [i for i in range(n) if not step2[i]]
+
+
+@pytest.mark.gpu
+def test_prefilter_nodes_rebuilds_until_no_node_is_disconnected():
+    """RecoverEngine::prefilter_nodes (recover_engine.rs:464-482).  As the reference stands (filters dropped) an exact
+    graph has no disconnected node and one build is enough.  With the filters applied, the loop removes the
+    disconnected contigs from all tables, rebuilds, and from round `rounds` + 1 on keeps n_neighbours edges, which ends
+    it.  Modelled here with the building block tested above (EmbedderEngine::build_mutual_kgraph on the filtered
+    tables); the driver must land on the same graph, the same survivors and the same number of builds."""
+    n, s, k = 700, 4, 12
+    tnf, cov, _ = synth.knn_tables(n, s, seed=29)
+    for j, row in enumerate((100, 350, 600)):                # three contigs far from everything: every distance is 1.0,
+        cov[row, 0::2] = 1e4 * (j + 1)                       # so nobody lists them and none of their edges is mutual
+        cov[row, 1::2] = 1.0
+    names = [f"c{i}" for i in range(n)]
+    eng = host.RecoverEngine(cov, tnf, names, n_neighbours=k)
+    g = eng.prefilter_nodes(rounds=1)
+    assert eng.prefilter_rounds == 1 and eng.n_contigs == n and eng.n_filtered == 0 and g.nb_nodes == n
+    ref = host.build_mutual_kgraph(tnf, cov, keep_n_edges=0, n_neighbours=k)
+    assert all(np.array_equal(g.neighbours(i)[0], ref.neighbours(i)[0]) for i in range(0, n, 7))
+    for rounds in (1, 2):
+        eng = host.RecoverEngine(cov, tnf, names, n_neighbours=k, apply_filters=True)
+        g = eng.prefilter_nodes(rounds=rounds)
+        rows, builds, current_round, keep_n = list(range(n)), 1, 1, 0
+        m = host.build_mutual_kgraph(tnf[rows], cov[rows], keep_n_edges=0, n_neighbours=k, apply_filters=True)
+        assert {100, 350, 600} <= set(m.disconnected_nodes)
+        while m.disconnected_nodes:
+            gone = set(m.disconnected_nodes)
+            rows = [r for p, r in enumerate(rows) if p not in gone]
+            current_round += 1
+            if current_round > rounds:
+                keep_n += k
+            m = host.build_mutual_kgraph(tnf[rows], cov[rows], keep_n_edges=keep_n, n_neighbours=k, apply_filters=True)
+            builds += 1
+        assert eng.prefilter_rounds == builds and eng.n_contigs == len(rows) and eng.names() == [names[r] for r in rows]
+        assert eng.n_filtered == n - len(rows) and all(eng.is_filtered(names[r]) for r in set(range(n)) - set(rows))
+        assert g.nb_nodes == len(rows) and g.disconnected_nodes == []
+        for i in range(len(rows)):
+            a, wa = g.neighbours(i); b, wb = m.neighbours(i)
+            assert np.array_equal(a, b) and np.array_equal(wa, wb)
+    # the k clamp of :513-517: fewer than 10 k rows -> min(n / 2, k)
+    small = host.RecoverEngine(cov[:50], tnf[:50], names[:50], n_neighbours=30)
+    assert small.prefilter_nodes().max_nbng == 25
 
 
 @pytest.mark.gpu
