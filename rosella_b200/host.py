@@ -59,6 +59,7 @@ def load() -> C.CDLL:
         "rh_recover_retrieve": (C.c_long, [vp, C.POINTER(sz), sz, dp, dp, C.POINTER(C.c_long)]),
         "rh_recover_filter_contigs": (C.c_int, [vp, C.POINTER(sz), sz]),
         "rh_recover_prefilter_nodes": (vp, [C.c_int, vp, sz]),
+        "rh_recover_evaluate_subset_graph": (vp, [C.c_int, vp, C.POINTER(sz), sz, sz]),
         "rh_build_mutual_kgraph": (vp, [C.c_int, dp, sz, dp, sz, sz, sz, sz, sz, sz, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_double]),
         "rh_graph_free": (None, [vp]), "rh_graph_nb_nodes": (sz, [vp]), "rh_graph_max_nbng": (sz, [vp]),
@@ -335,6 +336,12 @@ class RecoverEngine:
         arr = (C.c_size_t * len(nodes))(*[int(i) for i in nodes])
         if load().rh_recover_filter_contigs(self._h, arr, len(nodes)):
             raise _err()
+
+    def evaluate_subset_graph(self, indices, keep_n_edges: int, device: int = 0) -> "KGraphResult":
+        """graph half of evaluate_subset (:410-435); .disconnected_nodes holds ORIGINAL row indices"""
+        idx = sorted(set(int(i) for i in indices))
+        arr = (C.c_size_t * len(idx))(*idx)
+        return KGraphResult(load().rh_recover_evaluate_subset_graph(device, self._h, arr, len(idx), keep_n_edges))
 
     def prefilter_nodes(self, rounds: int = 1, device: int = 0) -> "KGraphResult":
         return KGraphResult(load().rh_recover_prefilter_nodes(device, self._h, rounds))

@@ -236,6 +236,19 @@ int rh_recover_filter_contigs(RecoverEngine *r, const size_t *nodes, size_t n) {
         r->filter_contigs(g, std::vector<size_t>(nodes, nodes + n));
     });
 }
+// the disconnected list of the returned graph holds ORIGINAL row indices
+rh_graph *rh_recover_evaluate_subset_graph(int device, const RecoverEngine *r, const size_t *idx, size_t n, size_t keep_n_edges) {
+    rh_graph *out = nullptr;
+    if (guard([&] {
+            Gpu gpu(device);
+            auto p = std::make_unique<rh_graph>();
+            auto res = r->evaluate_subset_graph(gpu, std::set<size_t>(idx, idx + n), keep_n_edges);
+            p->g = std::move(res.first);
+            p->disconnected = std::move(res.second);
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
 rh_graph *rh_recover_prefilter_nodes(int device, RecoverEngine *r, size_t rounds) {
     rh_graph *out = nullptr;
     if (guard([&] {

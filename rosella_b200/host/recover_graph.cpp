@@ -69,6 +69,17 @@ std::pair<KGraph, std::vector<size_t>> RecoverEngine::build_mutual_kgraph(Gpu &g
     return embedder_engine.build_mutual_kgraph(gpu, keep_n_edges, k, n_contigs, max_layers, ef_construction, apply_filters, variant);
 }
 
+// :410-435, the part before the embedding: subset graph + its disconnected nodes mapped back to original rows (:424-426)
+std::pair<KGraph, std::vector<size_t>> RecoverEngine::evaluate_subset_graph(Gpu &gpu, const std::set<size_t> &original_contig_indices,
+                                                                            size_t keep_n_edges) const {
+    const std::vector<size_t> contig_id_map(original_contig_indices.begin(), original_contig_indices.end());   // position -> original
+    auto [subset_kgraph, disconnected_nodes] = build_mutual_kgraph(gpu, keep_n_edges, original_contig_indices);
+    std::vector<size_t> disconnected_indices;
+    for (size_t i : disconnected_nodes)
+        if (auto id = subset_kgraph.get_data_id_from_idx(i)) disconnected_indices.push_back(contig_id_map.at(*id));
+    return {std::move(subset_kgraph), std::move(disconnected_indices)};
+}
+
 // :485-505 node index -> data id -> the same row of the three tables
 void RecoverEngine::filter_contigs(const KGraph &kgraph, const std::vector<size_t> &disconnected_nodes) {
     std::set<size_t> original_indices;

@@ -180,6 +180,12 @@ class RecoverEngine {             // `no_flight` members of recover_engine.rs:48
     // :510-519 (k clamp :513-517); node i of the graph = the i-th included row
     std::pair<KGraph, std::vector<size_t>> build_mutual_kgraph(Gpu &gpu, size_t keep_n_edges,
                                                                const std::set<size_t> &indices_to_include) const;
+    // the graph half of evaluate_subset (:410-435; embedding and HDBSCAN are downstream): the graph of the included rows
+    // and its disconnected nodes as ORIGINAL row indices.  Node i is the i-th included row in ascending order — that is
+    // what retrieve_contig_data produces; the reference builds its position map from the HashSet's iteration order
+    // (:413), which only agrees with that by accident.
+    std::pair<KGraph, std::vector<size_t>> evaluate_subset_graph(Gpu &gpu, const std::set<size_t> &original_contig_indices,
+                                                                 size_t keep_n_edges) const;
     KGraph prefilter_nodes(Gpu &gpu, size_t rounds);                                      // :464-482
     void filter_contigs(const KGraph &kgraph, const std::vector<size_t> &disconnected_nodes);   // :485-505
 

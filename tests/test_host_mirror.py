@@ -319,6 +319,14 @@ def test_prefilter_nodes_rebuilds_until_no_node_is_disconnected():
         for i in range(len(rows)):
             a, wa = g.neighbours(i); b, wb = m.neighbours(i)
             assert np.array_equal(a, b) and np.array_equal(wa, wb)
+    # evaluate_subset's graph (:410-435): node i = the i-th included row, disconnected nodes come back as original rows
+    eng = host.RecoverEngine(cov, tnf, names, n_neighbours=k, apply_filters=True)
+    subset = sorted(set(range(40, 640, 2)) | {100, 350, 600})
+    sg = eng.evaluate_subset_graph(subset, keep_n_edges=0)
+    sm = host.build_mutual_kgraph(tnf[subset], cov[subset], keep_n_edges=0, n_neighbours=k, apply_filters=True)
+    assert sg.nb_nodes == len(subset) and sg.disconnected_nodes == [subset[p] for p in sm.disconnected_nodes]
+    assert {100, 350, 600} <= set(sg.disconnected_nodes)
+    assert all(np.array_equal(sg.neighbours(i)[0], sm.neighbours(i)[0]) for i in range(0, len(subset), 5))
     # the k clamp of :513-517: fewer than 10 k rows -> min(n / 2, k)
     small = host.RecoverEngine(cov[:50], tnf[:50], names[:50], n_neighbours=30)
     assert small.prefilter_nodes().max_nbng == 25
