@@ -12,7 +12,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "librosella_gpu.so")
 HOST_DIR = os.path.join(HERE, "host")
 HOST_LIB = os.path.join(HERE, "librosella_host.so")
-HOST_SOURCES = ["kmer_table.cpp", "fastx.cpp", "embedder.cpp", "sketcher.cpp", "recover_graph.cpp", "capi.cpp"]
+HOST_SOURCES = ["kmer_table.cpp", "fastx.cpp", "embedder.cpp", "sketcher.cpp", "recover_graph.cpp", "coverage_table.cpp", "capi.cpp"]
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall", "--expt-relaxed-constexpr"]

@@ -50,6 +50,13 @@ def load() -> C.CDLL:
         "rh_sketches_free": (None, [vp]), "rh_sketches_n": (sz, [vp]), "rh_sketches_name": (C.c_char_p, [vp, sz]),
         "rh_sketches_offsets": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_hashes": (C.POINTER(C.c_uint64), [vp]),
         "rh_sketches_num_valid_kmers": (C.POINTER(C.c_uint64), [vp]), "rh_sketches_seq_length": (C.POINTER(C.c_uint64), [vp]),
+        "rh_cov_from_file": (vp, [C.c_char_p, C.c_int]),
+        "rh_cov_new": (vp, [dp, sz, sz, C.POINTER(C.c_char_p), C.POINTER(sz), C.POINTER(C.c_char_p)]),
+        "rh_cov_free": (None, [vp]), "rh_cov_write": (C.c_int, [vp, C.c_char_p]), "rh_cov_merge": (C.c_int, [vp, vp]),
+        "rh_cov_filter_by_length": (C.c_long, [vp, sz]), "rh_cov_nrows": (sz, [vp]), "rh_cov_ncols": (sz, [vp]),
+        "rh_cov_n_samples": (sz, [vp]), "rh_cov_data": (dp, [vp]), "rh_cov_average_depths": (dp, [vp]),
+        "rh_cov_lengths": (C.POINTER(sz), [vp]), "rh_cov_name": (C.c_char_p, [vp, sz]), "rh_cov_sample": (C.c_char_p, [vp, sz]),
+        "rh_cov_path": (C.c_char_p, [vp]),
         "rh_recover_new": (vp, [dp, sz, sz, dp, sz, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), sz, C.c_int,
                                 C.c_uint32, C.c_double]),
         "rh_recover_free": (None, [vp]), "rh_recover_n_contigs": (sz, [vp]), "rh_recover_prefilter_rounds": (sz, [vp]),
@@ -264,6 +271,81 @@ class KGraphResult:
         if getattr(self, "_h", None) and _lib is not None:
             _lib.rh_graph_free(self._h)
             self._h = None
+
+
+SHORT_READ, LONG_READ, SHORT_BAM, LONG_BAM = 0, 1, 2, 3          # MappingMode, coverm_engine.rs:217-222
+
+
+class CoverageTable:
+    """src/coverage/coverage_table.rs: coverm's TSV <-> the n x 2S table the coverage metric reads"""
+
+    def __init__(self, handle):
+        if not handle:
+            raise _err()
+        self._h = handle
+
+    @classmethod
+    def from_file(cls, path: str, mode: int = SHORT_BAM):
+        return cls(load().rh_cov_from_file(path.encode(), mode))
+
+    @classmethod
+    def new(cls, table, names, lengths, samples):
+        t = np.ascontiguousarray(table, np.float64)
+        na = (C.c_char_p * len(names))(*[s.encode() for s in names])
+        sa = (C.c_char_p * len(samples))(*[s.encode() for s in samples])
+        la = (C.c_size_t * len(lengths))(*[int(x) for x in lengths])
+        return cls(load().rh_cov_new(t.ctypes.data_as(C.POINTER(C.c_double)), t.shape[0], t.shape[1], na, la, sa))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            load().rh_cov_free(self._h)
+            self._h = None
+
+    def write(self, path: str):
+        if load().rh_cov_write(self._h, path.encode()):
+            raise _err()
+
+    def merge(self, other: "CoverageTable"):
+        if load().rh_cov_merge(self._h, other._h):
+            raise _err()
+
+    def filter_by_length(self, min_contig_size: int) -> int:
+        r = load().rh_cov_filter_by_length(self._h, min_contig_size)
+        if r < 0:
+            raise _err()
+        return r
+
+    @property
+    def table(self) -> np.ndarray:
+        lib = load()
+        n, c = lib.rh_cov_nrows(self._h), lib.rh_cov_ncols(self._h)
+        return np.ctypeslib.as_array(lib.rh_cov_data(self._h), (n * c,)).copy().reshape(n, c) if n * c else np.zeros((n, c))
+
+    @property
+    def average_depths(self) -> np.ndarray:
+        lib = load()
+        n = lib.rh_cov_nrows(self._h)
+        return np.ctypeslib.as_array(lib.rh_cov_average_depths(self._h), (n,)).copy() if n else np.zeros(0)
+
+    @property
+    def contig_lengths(self):
+        lib = load()
+        n = lib.rh_cov_nrows(self._h)
+        return [lib.rh_cov_lengths(self._h)[i] for i in range(n)]
+
+    @property
+    def contig_names(self):
+        lib = load()
+        return [lib.rh_cov_name(self._h, i).decode() for i in range(lib.rh_cov_nrows(self._h))]
+
+    @property
+    def sample_names(self):
+        lib = load()
+        return [lib.rh_cov_sample(self._h, i).decode() for i in range(lib.rh_cov_n_samples(self._h))]
+
+    @property
+    def output_path(self) -> str:
+        return load().rh_cov_path(self._h).decode()
 
 
 class RecoverEngine:

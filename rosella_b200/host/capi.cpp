@@ -164,6 +164,52 @@ const uint64_t *rh_sketches_hashes(const rh_sketches *s) { return s->hashes.data
 const uint64_t *rh_sketches_num_valid_kmers(const rh_sketches *s) { return s->num_valid_kmers.data(); }
 const uint64_t *rh_sketches_seq_length(const rh_sketches *s) { return s->seq_length.data(); }
 
+// ---------------------------------------------------------------- CoverageTable
+CoverageTable *rh_cov_from_file(const char *path, int mode) {
+    CoverageTable *t = nullptr;
+    if (guard([&] {
+            if (mode < 0 || mode > 3) throw Error("rh_cov_from_file: mode must be 0 ShortRead, 1 LongRead, 2 ShortBam, 3 LongBam");
+            t = new CoverageTable(CoverageTable::from_file(path, (MappingMode)mode));
+        })) return nullptr;
+    return t;
+}
+CoverageTable *rh_cov_new(const double *table, size_t nrows, size_t ncols, const char *const *names, const size_t *lengths,
+                          const char *const *samples) {
+    CoverageTable *t = nullptr;
+    if (guard([&] {
+            auto p = std::make_unique<CoverageTable>();
+            p->nrows = nrows; p->ncols = ncols;
+            p->table.assign(table, table + nrows * ncols);
+            for (size_t i = 0; i < nrows; ++i) {
+                p->contig_names.emplace_back(names[i]);
+                p->contig_lengths.push_back(lengths[i]);
+                double sum = 0.0;
+                for (size_t j = 0; j < ncols; j += 2) sum += table[i * ncols + j];
+                p->average_depths.push_back(ncols ? sum / (double)(ncols / 2) : 0.0);
+            }
+            for (size_t j = 0; j < ncols / 2; ++j) p->sample_names.emplace_back(samples[j]);
+            t = p.release();
+        })) return nullptr;
+    return t;
+}
+void rh_cov_free(CoverageTable *t) { delete t; }
+int rh_cov_write(CoverageTable *t, const char *path) { return guard([&] { t->write(path); }); }
+int rh_cov_merge(CoverageTable *t, const CoverageTable *other) { return guard([&] { t->merge(*other); }); }
+long rh_cov_filter_by_length(CoverageTable *t, size_t min_contig_size) {
+    long removed = -1;
+    if (guard([&] { removed = (long)t->filter_by_length(min_contig_size).size(); })) return -1;
+    return removed;
+}
+size_t rh_cov_nrows(const CoverageTable *t) { return t->nrows; }
+size_t rh_cov_ncols(const CoverageTable *t) { return t->ncols; }
+size_t rh_cov_n_samples(const CoverageTable *t) { return t->sample_names.size(); }
+const double *rh_cov_data(const CoverageTable *t) { return t->table.data(); }
+const double *rh_cov_average_depths(const CoverageTable *t) { return t->average_depths.data(); }
+const size_t *rh_cov_lengths(const CoverageTable *t) { return t->contig_lengths.data(); }
+const char *rh_cov_name(const CoverageTable *t, size_t i) { return t->contig_names.at(i).c_str(); }
+const char *rh_cov_sample(const CoverageTable *t, size_t i) { return t->sample_names.at(i).c_str(); }
+const char *rh_cov_path(const CoverageTable *t) { return t->output_path.c_str(); }
+
 // ---------------------------------------------------------------- RecoverEngine's graph driver
 RecoverEngine *rh_recover_new(const double *cov, size_t n, size_t c, const double *tnf, size_t d, const char *const *names,
                               const uint64_t *sketch_offsets, const uint64_t *sketch_hashes, size_t n_neighbours, int apply_filters,

@@ -162,14 +162,24 @@ class EmbedderEngine {        // embedder.rs:15-87
 };
 
 // ------------------------------------------------------------------ RecoverEngine's graph driver (recover_engine.rs:407-543)
-struct CoverageTable {            // src/coverage/coverage_table.rs:9-17, the members the path touches
-    size_t nrows = 0, ncols = 0;                 // ncols = 2 x samples: mean, variance interleaved
+enum class MappingMode { ShortRead, LongRead, ShortBam, LongBam };   // src/external/coverm_engine.rs:217-222
+struct CoverageTable {            // src/coverage/coverage_table.rs:9-17
+    size_t nrows = 0, ncols = 0;                 // ncols = 2 x samples; MetabatDistance reads mean, variance interleaved
     std::vector<double> table;                   // row-major
     std::vector<double> average_depths;
     std::vector<std::string> contig_names;
     std::vector<size_t> contig_lengths;
+    std::vector<std::string> sample_names;
+    std::string output_path;
     const double *row(size_t i) const { return table.data() + i * ncols; }
+    std::set<std::string> filter_by_length(size_t min_contig_size);                      // :38-52
+    std::set<std::string> get_contig_names(const std::set<size_t> &indices) const;       // :54-67
     std::set<std::string> filter_by_index(const std::set<size_t> &indices_to_remove);   // :69-131, returns the removed names
+    // :135-284 coverm's TSV; a row comes out as [cov_1..cov_S, var_1..var_S], long-read tables of S > 1 fail
+    static CoverageTable from_file(const std::string &file_path, MappingMode mode);
+    void merge(const CoverageTable &other);                                              // :286-308
+    static CoverageTable merge_many(std::vector<CoverageTable> coverage_tables);         // :315-329
+    void write(const std::string &output_path);                                          // :335-377, values as {:.3}
 };
 
 class RecoverEngine {             // `no_flight` members of recover_engine.rs:48-75 that the graph driver uses
