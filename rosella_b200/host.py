@@ -59,6 +59,8 @@ def load() -> C.CDLL:
         "rh_cov_path": (C.c_char_p, [vp]),
         "rh_recover_new": (vp, [dp, sz, sz, dp, sz, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), sz, C.c_int,
                                 C.c_uint32, C.c_double]),
+        "rh_recover_from_files": (vp, [C.c_int, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, sz, sz, C.c_int]),
+        "rh_recover_cov_cols": (sz, [vp]), "rh_recover_tnf_cols": (sz, [vp]),
         "rh_recover_free": (None, [vp]), "rh_recover_n_contigs": (sz, [vp]), "rh_recover_prefilter_rounds": (sz, [vp]),
         "rh_recover_n_filtered": (sz, [vp]), "rh_recover_is_filtered": (C.c_int, [vp, C.c_char_p]),
         "rh_recover_name": (C.c_char_p, [vp, sz]), "rh_recover_tnf_name": (C.c_char_p, [vp, sz]),
@@ -368,6 +370,20 @@ class RecoverEngine:
                                         n_neighbours, int(apply_filters), variant, sketch_scale)
         if not self._h:
             raise _err()
+
+    @classmethod
+    def from_files(cls, assembly: str, output_directory: str, coverage_file: str, mode: int = 2, kmer_frequency_file=None,
+                   min_contig_size: int = 1500, n_neighbours: int = 100, apply_filters: bool = False, device: int = 0):
+        """RecoverEngine::new (recover_engine.rs:93-131) without the coverm subprocess"""
+        self = cls.__new__(cls)
+        lib = load()
+        self._h = lib.rh_recover_from_files(device, assembly.encode(), output_directory.encode(), coverage_file.encode(), mode,
+                                            kmer_frequency_file.encode() if kmer_frequency_file else None, min_contig_size,
+                                            n_neighbours, int(apply_filters))
+        if not self._h:
+            raise _err()
+        self._c, self._d = lib.rh_recover_cov_cols(self._h), lib.rh_recover_tnf_cols(self._h)
+        return self
 
     def __del__(self):
         if getattr(self, "_h", None):

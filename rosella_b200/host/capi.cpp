@@ -247,6 +247,27 @@ RecoverEngine *rh_recover_new(const double *cov, size_t n, size_t c, const doubl
         })) return nullptr;
     return out;
 }
+// kmer_frequency_file may be NULL (count on the GPU)
+RecoverEngine *rh_recover_from_files(int device, const char *assembly, const char *output_directory, const char *coverage_file, int mode,
+                                     const char *kmer_frequency_file, size_t min_contig_size, size_t n_neighbours, int apply_filters) {
+    RecoverEngine *out = nullptr;
+    if (guard([&] {
+            if (mode < 0 || mode > 3) throw Error("rh_recover_from_files: mode must be 0..3");
+            Gpu gpu(device);
+            RecoverArgs m;
+            m.assembly = assembly; m.output_directory = output_directory; m.coverage_file = coverage_file;
+            m.coverage_mode = (MappingMode)mode;
+            if (kmer_frequency_file) m.kmer_frequency_file = std::string(kmer_frequency_file);
+            m.min_contig_size = min_contig_size;
+            m.n_neighbours = n_neighbours;
+            auto p = std::make_unique<RecoverEngine>(RecoverEngine::from_files(gpu, m));
+            p->apply_filters = apply_filters != 0;
+            out = p.release();
+        })) return nullptr;
+    return out;
+}
+size_t rh_recover_cov_cols(const RecoverEngine *r) { return r->coverage_table.ncols; }
+size_t rh_recover_tnf_cols(const RecoverEngine *r) { return r->tnf_table.ncols; }
 void rh_recover_free(RecoverEngine *r) { delete r; }
 size_t rh_recover_n_contigs(const RecoverEngine *r) { return r->n_contigs; }
 size_t rh_recover_prefilter_rounds(const RecoverEngine *r) { return r->prefilter_rounds; }

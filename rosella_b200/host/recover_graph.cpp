@@ -3,6 +3,7 @@
 // filter_contigs (:485-505), and CoverageTable::filter_by_index (src/coverage/coverage_table.rs:69-131).
 // The graphs come from EmbedderEngine (embedder.cpp), i.e. from the GPU; everything else here is host bookkeeping.
 #include <algorithm>
+#include <filesystem>
 
 #include "rosella_host.hpp"
 
@@ -39,6 +40,30 @@ RecoverEngine::RecoverEngine(CoverageTable coverage, KmerFrequencyTable tnf, Con
     if (tnf_table.nrows != n_contigs) throw Error("RecoverEngine: the TNF table and the coverage table differ in rows");
     if (!contig_sketches.contig_sketches.empty() && contig_sketches.contig_sketches.size() != n_contigs)
         throw Error("RecoverEngine: one sketch per contig is required (or none at all)");
+}
+
+// recover_engine.rs:93-131
+RecoverEngine RecoverEngine::from_files(Gpu &gpu, const RecoverArgs &m) {
+    std::error_code ec;
+    std::filesystem::create_directories(m.output_directory, ec);                         // :92 create_dir_all
+    if (ec) throw Error("RecoverEngine: cannot create " + m.output_directory + ": " + ec.message());
+    CoverageTable coverage_table = CoverageTable::from_file(m.coverage_file, m.coverage_mode);   // :95 (coverage_calculator.rs:90)
+    const size_t n_contigs = coverage_table.nrows;                                       // :96
+    const std::set<std::string> filtered_contigs = coverage_table.filter_by_length(m.min_contig_size);   // :99
+    if (coverage_table.nrows != n_contigs - filtered_contigs.size())                     // :104
+        throw Error("Coverage table row count and total contigs minus filtered contigs do not match.");
+    KmerFrequencyTable tnf_table = m.kmer_frequency_file ? KmerFrequencyTable::read(*m.kmer_frequency_file, true)     // :105-107
+                                                         : count_kmers(gpu, CountKmersArgs{m.assembly, m.output_directory}, n_contigs, true);   // :110
+    if (n_contigs != tnf_table.nrows) throw Error("Coverage table row count and TNF table row count do not match.");   // :112
+    tnf_table.filter_by_name(filtered_contigs);                                          // :114
+    if (coverage_table.nrows != tnf_table.nrows) throw Error("Coverage table and TNF table have different number of contigs.");   // :115
+    ContigSketchResult contig_sketches = sketch_contigs(gpu, SketchContigsArgs{m.assembly, m.min_contig_size, m.sketch_settings});  // :120
+    if (coverage_table.nrows != contig_sketches.contig_sketches.size())                 // :122
+        throw Error("Coverage table and contig sketches have different number of contigs.");
+    RecoverEngine e(std::move(coverage_table), std::move(tnf_table), std::move(contig_sketches));
+    e.n_neighbours = m.n_neighbours; e.max_layers = m.max_layers; e.ef_construction = m.ef_construction;
+    e.sketch_scale = m.sketch_settings.sketch_scale;
+    return e;                                                                            // :140 filtered_contigs starts empty
 }
 
 // :522-543 one ContigInformation per included row, in row order (borrowed views into the three tables)

@@ -182,9 +182,23 @@ struct CoverageTable {            // src/coverage/coverage_table.rs:9-17
     void write(const std::string &output_path);                                          // :335-377, values as {:.3}
 };
 
+struct RecoverArgs {              // the clap arguments RecoverEngine::new reads for the three tables (recover_engine.rs:76-131)
+    std::string assembly, output_directory;
+    std::string coverage_file;                   // --coverage-file: calculate_coverage reads it as MappingMode::ShortBam
+    MappingMode coverage_mode = MappingMode::ShortBam;   // (coverage_calculator.rs:90); running coverm itself is out of scope
+    std::optional<std::string> kmer_frequency_file;
+    size_t min_contig_size = 1500;
+    SketchSettings sketch_settings;
+    size_t n_neighbours = 100, max_layers = 16, ef_construction = 100;
+};
+
 class RecoverEngine {             // `no_flight` members of recover_engine.rs:48-75 that the graph driver uses
    public:
     RecoverEngine(CoverageTable coverage, KmerFrequencyTable tnf, ContigSketchResult sketches);
+    // RecoverEngine::new (:93-131) without the coverm subprocess: coverage table from its file, filter_by_length, TNF table
+    // read or counted on the GPU (CLR applied, `no_flight`), filtered by the removed names, sketches on the GPU; the
+    // reference's assert_eq! checks become Errors with the same messages
+    static RecoverEngine from_files(Gpu &gpu, const RecoverArgs &m);
     // :522-543
     std::vector<std::vector<ContigInformation>> retrieve_contig_data(const std::set<size_t> &indices_to_include) const;
     // :510-519 (k clamp :513-517); node i of the graph = the i-th included row

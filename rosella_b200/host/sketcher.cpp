@@ -8,12 +8,16 @@ namespace rosella {
 
 ContigSketchResult sketch_contigs(Gpu &gpu, const SketchContigsArgs &m) {
     FastxRecords rec = parse_fastx_file(m.assembly);                         // :48
-    // :53-55 records shorter than min_contig_size are skipped (raw sequence length, as seqrec.seq().len())
+    // :53-55 records shorter than min_contig_size are skipped.  seqrec.seq().len(): needletail's seq() is the record's
+    // sequence without its line terminators (raw_seq() would keep them), so a 60-column FASTA record counts its bases,
+    // not its bytes
     FastxRecords kept;
     kept.offsets.push_back(0);
     for (size_t i = 0; i < rec.ids.size(); ++i) {
         const uint64_t b = rec.offsets[i], e = rec.offsets[i + 1];
-        if (e - b < m.min_contig_size) continue;
+        uint64_t seq_len = 0;
+        for (uint64_t p = b; p < e; ++p) seq_len += !(rec.seq[p] == '\n' || rec.seq[p] == '\r');
+        if (seq_len < m.min_contig_size) continue;
         kept.ids.push_back(rec.ids[i]);
         kept.seq.insert(kept.seq.end(), rec.seq.begin() + (std::ptrdiff_t)b, rec.seq.begin() + (std::ptrdiff_t)e);
         kept.offsets.push_back(kept.seq.size());

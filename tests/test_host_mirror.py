@@ -239,7 +239,7 @@ def test_sketch_contigs_matches_the_oracle(tmp_path):
     _write_fasta(fa, ids, seqs)
     names, hashes, so, nk, sl = host.sketch_contigs(fa, min_contig_size=1500)
     got_ids, raw, roffs = host.parse_fastx_file(fa)                 # the raw records (with their line breaks)
-    keep = [i for i in range(len(got_ids)) if int(roffs[i + 1] - roffs[i]) >= 1500]
+    keep = [i for i in range(len(got_ids)) if len(seqs[i]) >= 1500]         # seq().len(): bases, not bytes with line breaks
     assert names == [got_ids[i] for i in keep] and 0 < len(keep) < len(ids)
     recs = [bytes(raw[int(roffs[i]):int(roffs[i + 1])]) for i in keep]
     koffs = np.zeros(len(recs) + 1, np.uint64); koffs[1:] = np.cumsum([len(r) for r in recs])
@@ -330,6 +330,47 @@ def test_prefilter_nodes_rebuilds_until_no_node_is_disconnected():
     # the k clamp of :513-517: fewer than 10 k rows -> min(n / 2, k)
     small = host.RecoverEngine(cov[:50], tnf[:50], names[:50], n_neighbours=30)
     assert small.prefilter_nodes().max_nbng == 25
+
+
+@pytest.mark.gpu
+def test_recover_engine_from_files(tmp_path):
+    """RecoverEngine::new (recover_engine.rs:93-131) without the coverm subprocess: coverage file -> filter_by_length ->
+    TNF table counted on the GPU (CLR applied) and filtered by the removed names -> sketches on the GPU; the three tables
+    must describe the same contigs in the same order, and the graph driver runs on them."""
+    seq, offs = synth.contigs(500_000, threads=2, min_len=600, max_len=9000, seed=41)
+    n = len(offs) - 1
+    ids = [f"k141_{i}" for i in range(n)]
+    seqs = [bytes(seq[int(offs[i]):int(offs[i + 1])]).decode() for i in range(n)]
+    lengths = [len(x) for x in seqs]
+    fa = str(tmp_path / "assembly.fna")
+    _write_fasta(fa, ids, seqs)
+    _, cov, _ = synth.knn_tables(n, 2, seed=8)
+    cf = str(tmp_path / "coverage.tsv")
+    with open(cf, "w") as f:
+        f.write("contigName\tcontigLen\ttotalAvgDepth\tassembly.fna/s1.bam\ts1-var\tassembly.fna/s2.bam\ts2-var\n")
+        for i in range(n):
+            f.write("\t".join([ids[i], str(lengths[i]), repr(float(cov[i, 0::2].mean()))] + [repr(float(x)) for x in cov[i]]) + "\n")
+    out = str(tmp_path / "out" / "nested")
+    eng = host.RecoverEngine.from_files(fa, out, cf, min_contig_size=1500, n_neighbours=10)
+    keep = [i for i in range(n) if lengths[i] >= 1500]
+    assert 0 < len(keep) < n and eng.n_contigs == len(keep) and eng.names() == [ids[i] for i in keep]
+    c, t, sl = eng.tables()
+    assert np.array_equal(c, np.hstack([cov[keep][:, 0::2], cov[keep][:, 1::2]]))          # rows as from_file hands them (F6)
+    _, _, freq = oracle.tnf_count(seq, offs, fast=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        assert np.array_equal(t, oracle.clr(freq)[keep], equal_nan=True)
+    koffs = np.zeros(len(keep) + 1, np.uint64); koffs[1:] = np.cumsum([lengths[i] for i in keep])
+    kseq = np.frombuffer("".join(seqs[i] for i in keep).encode(), np.uint8)
+    _, wo, _, _ = oracle.sketch_contigs(kseq, koffs)
+    assert sl == list(np.diff(wo.astype(np.int64)))
+    assert os.path.exists(os.path.join(out, "kmer_frequencies.tsv"))
+    g = eng.prefilter_nodes(rounds=1)
+    assert g.nb_nodes == len(keep) and g.max_nbng == 10 and eng.prefilter_rounds == 1
+    # a coverage file that lists other contigs than the assembly: the reference's assert_eq! messages come back as errors
+    with open(cf, "a") as f:
+        f.write("\t".join(["extra", "5000", "1.0", "1.0", "1.0", "1.0", "1.0"]) + "\n")
+    with pytest.raises(host.HostError, match="TNF table row count"):
+        host.RecoverEngine.from_files(fa, str(tmp_path / "out2"), cf, min_contig_size=1500)
 
 
 @pytest.mark.gpu
