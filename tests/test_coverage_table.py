@@ -151,3 +151,33 @@ def test_write_round_trip_merge_and_length_filter(tmp_path):
     c.write(p)
     rows = list(csv.reader(open(p, newline=""), delimiter="\t"))
     assert rows[1][3:] == ["NaN", "inf"] and rows[2][3:] == ["-0.000", _rust_fixed3(2.0005)]
+
+
+def test_write_then_read_property(tmp_path):
+    """write -> from_file over generated tables (hypothesis, derandomised): every value comes back as the number its
+    {:.3} text denotes, names with quotes / tabs survive the csv quoting, rows come back coverages-then-variances."""
+    from hypothesis import given, settings, strategies as st
+
+    name = st.text(alphabet=st.sampled_from(list("abcXYZ019_.|=\" \t")), min_size=1, max_size=12).filter(lambda x: x.strip() == x and x != "")
+    value = st.one_of(st.floats(min_value=-1e6, max_value=1e9, allow_nan=False), st.sampled_from([0.0, -0.0, 0.0005, 0.0015, 1e-9, 123456.7895]))
+    counter = [0]
+
+    @settings(derandomize=True, max_examples=40, deadline=None)
+    @given(st.integers(1, 5), st.integers(1, 3), st.data())
+    def run(n, s, data):
+        names = data.draw(st.lists(name, min_size=n, max_size=n, unique=True))
+        samples = data.draw(st.lists(name.filter(lambda x: "/" not in x), min_size=s, max_size=s))
+        table = np.array(data.draw(st.lists(st.lists(value, min_size=2 * s, max_size=2 * s), min_size=n, max_size=n)))
+        lengths = data.draw(st.lists(st.integers(0, 10 ** 9), min_size=n, max_size=n))
+        t = host.CoverageTable.new(table, names, lengths, samples)
+        counter[0] += 1
+        p = str(tmp_path / f"t{counter[0]}.tsv")
+        t.write(p)
+        back = host.CoverageTable.from_file(p)
+        rounded = np.array([[float(_rust_fixed3(v)) for v in row] for row in table])
+        assert np.array_equal(back.table, np.hstack([rounded[:, 0::2], rounded[:, 1::2]]))
+        assert back.contig_names == names and back.contig_lengths == lengths and back.sample_names == samples
+        want, wn, wl, wd, ws = _model_from_file(p, False)
+        assert np.array_equal(back.table, want) and wn == names and ws == samples
+
+    run()
