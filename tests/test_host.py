@@ -162,3 +162,21 @@ def test_register_classifier_model_of_the_ascii_tnf_kernel():
     for _ in range(50000):
         w = rnd.getrandbits(32)
         assert ((classify4(w)[1] & 0xDFDFDFDF) == 0) == all(((w >> (8 * i)) & 0xFF) in code for i in range(4))
+
+
+def test_integration_doc_binds_every_entry_point():
+    """INTEGRATION.md promises an `extern "C"` block 1:1 with include/rosella_gpu.h: every declared entry point has its
+    `pub fn` there, and nothing else does."""
+    hdr = open(os.path.join(ROOT, "include", "rosella_gpu.h")).read()
+    declared = set(re.findall(r"\b(rg_[a-z0-9_]+)\s*\(", hdr)) - {"rg_handle"}
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    bound = set(re.findall(r"pub fn (rg_[a-z0-9_]+)", doc))
+    assert bound == declared, bound ^ declared
+    # the two instrumentation structs mirror the header field for field
+    for c_name, rust_name in (("rg_timings", "RgTimings"), ("rg_dist_timings", "RgDistTimings")):
+        body = re.search(r"typedef struct \{([^}]*)\} " + c_name + ";", hdr).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        c_fields = [f.strip() for decl in body.split(";") if decl.strip() for f in decl.strip().split(None, 1)[1].split(",")]
+        rust = re.search(r"pub struct " + rust_name + r" \{(.*?)\n\}", doc, re.S).group(1)
+        rust = re.sub(r"//.*", "", rust)
+        assert re.findall(r"pub (\w+):", rust) == c_fields, (c_name, c_fields)
