@@ -24,6 +24,22 @@ def shard_range(n: int, rank: int, world: int, align: int = TILE) -> tuple[int, 
     return min(t0 * align, n), min(t1 * align, n)
 
 
+def record_cuts(offsets, world: int) -> list[int]:
+    """The record ranges of rg_multi_tnf_count_ascii / rg_multi_sketch_contigs (csrc/rg_multi.cu) restated: rank r owns
+    records [cuts[r], cuts[r + 1]) — contiguous, in order, about total / world bytes each (the first record whose start
+    reaches r * (total / world)); no record is split, so per-record results only need concatenating."""
+    offsets = np.asarray(offsets, np.uint64)
+    n = len(offsets) - 1
+    cuts = [0] * (world + 1)
+    if n:
+        base0, total = int(offsets[0]), int(offsets[n]) - int(offsets[0])
+        for r in range(1, world):
+            target = base0 + total // world * r
+            cuts[r] = min(max(cuts[r - 1], int(np.searchsorted(offsets, np.uint64(target), side="left"))), n)
+    cuts[world] = n
+    return cuts
+
+
 def init_comm(ctx, rank: int, world: int, group=None):
     """rg_comm_init on every rank: rank 0's ncclUniqueId travels through torch.distributed (any backend)."""
     import torch

@@ -59,6 +59,69 @@ def test_gloo_world2_all_gather_matches_single_process(tmp_path):
     assert np.array_equal(got["idx"], idx) and np.array_equal(got["dist"], dst)
 
 
+def test_record_cuts_are_contiguous_and_balanced():
+    rng = np.random.default_rng(8)
+    for n in (0, 1, 2, 7, 500):
+        lens = rng.integers(0, 5000, n)
+        offs = np.zeros(n + 1, np.uint64); offs[1:] = np.cumsum(lens)
+        offs += np.uint64(17)                                          # a table that does not start at byte 0
+        for world in (1, 2, 3, 8):
+            cuts = rdist.record_cuts(offs, world)
+            assert cuts[0] == 0 and cuts[-1] == n and all(a <= b for a, b in zip(cuts, cuts[1:]))
+            if n >= 200:
+                share = [int(offs[b]) - int(offs[a]) for a, b in zip(cuts, cuts[1:])]
+                assert max(share) - min(share) <= 2 * 5000
+
+
+def _worker_records(rank, world, port, total_bp, out):
+    """Every rank counts TNF and sketches ITS record range (the oracle stands in for the device) — no exchange on the
+    data path; rank 0 only concatenates."""
+    import torch.distributed as dist
+
+    import oracle
+    from rosella_b200 import synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    seq, offs = synth.contigs(total_bp, threads=1, seed=3)
+    cuts = rdist.record_cuts(offs, world)
+    a, b = cuts[rank], cuts[rank + 1]
+    local_seq = seq[int(offs[a]):int(offs[b])]
+    local_offs = offs[a:b + 1] - offs[a]
+    counts, nk, _ = oracle.tnf_count(local_seq, local_offs, fast=True)
+    h, so, snk, _ = oracle.sketch_contigs(local_seq, local_offs)
+    parts = [None] * world
+    dist.all_gather_object(parts, (counts, nk, h, so, snk))
+    if rank == 0:
+        sk_off = [np.zeros(1, np.uint64)]
+        for p in parts:
+            sk_off.append(p[3][1:] + sk_off[-1][-1])
+        np.savez(out, counts=np.concatenate([p[0] for p in parts]), nk=np.concatenate([p[1] for p in parts]),
+                 hashes=np.concatenate([p[2] for p in parts]), sk_off=np.concatenate(sk_off), snk=np.concatenate([p[4] for p in parts]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_record_ranges_need_no_exchange(tmp_path):
+    """TNF counting and MinHash sketching on N ranks: contiguous record ranges, results concatenated."""
+    import torch.multiprocessing as mp
+
+    import oracle
+    from rosella_b200 import synth
+    world, total_bp = 2, 300_000
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = str(tmp_path / "records.npz")
+    mp.spawn(_worker_records, args=(world, port, total_bp, out), nprocs=world, join=True)
+    got = np.load(out)
+    seq, offs = synth.contigs(total_bp, threads=1, seed=3)
+    counts, nk, _ = oracle.tnf_count(seq, offs, fast=True)
+    h, so, snk, _ = oracle.sketch_contigs(seq, offs)
+    assert np.array_equal(got["counts"], counts) and np.array_equal(got["nk"], nk)
+    assert np.array_equal(got["hashes"], h) and np.array_equal(got["sk_off"], so) and np.array_equal(got["snk"], snk)
+
+
 def _worker_sym(rank, world, port, n, k, kp, out):
     """Partial lists of a pair partition (numpy stand-in for rg_knn_depth_partial_dev), exchanged with
     exchange_partial_lists, merged by (distance, index) (stand-in for rg_knn_depth_merge_dev), all-gathered."""
